@@ -1,0 +1,154 @@
+/*
+ * vsann.h — C ABI of the B200-native ANN index (drop-in for the usearch calls of
+ * the reference's index actor).
+ *
+ * Every entry point names the reference interface it replaces. Citations are
+ * relative to the reference tree (swasik/vector-store-text):
+ *   src/index/usearch.rs  — the orphaned usearch backend (the hot path)
+ *   src/lib.rs            — domain newtypes (Dimensions, Connectivity, ...)
+ *
+ * Conventions
+ *   - plain pointers + sizes, no C++/torch types; status codes, never exceptions
+ *   - all pointers are HOST memory unless the function name ends in `_device`
+ *   - caller keeps ownership of every buffer; inputs are copied/staged before return
+ *   - thread-safe: any number of host threads may call into one index concurrently
+ *     (the reference holds the library under Arc<RwLock<_>>, usearch.rs:98,201-221,245,276,309)
+ *   - the GPU library has NO CPU fallback: if no CUDA device is usable,
+ *     vs_index_create fails with VS_ERR_CUDA.
+ *
+ * Two libraries export this ABI:
+ *   libvsann.so          (vector-store-text_b200/csrc)  — the product, sm_100a CUDA
+ *   liboracle_vsann.so   (oracle/)                       — test-only CPU restatement,
+ *                                                          same signatures with an `o` prefix (ovs_*)
+ */
+#ifndef VSANN_H
+#define VSANN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vs_index vs_index;
+
+typedef enum vs_status {
+    VS_OK = 0,
+    VS_ERR_INVALID = 1,     /* null pointer / bad option / k == 0                      */
+    VS_ERR_DIMS = 2,        /* wrong embedding length  (usearch.rs:259-272)             */
+    VS_NOT_FOUND = 3,       /* remove of an unknown key — non-fatal (usearch.rs:245-247)*/
+    VS_ERR_CAPACITY = 4,    /* reserve failed (usearch.rs:206-210)                      */
+    VS_ERR_CUDA = 5,        /* CUDA runtime error / no device                           */
+    VS_ERR_NOMEM = 6,
+    VS_ERR_UNSUPPORTED = 7
+} vs_status;
+
+/* Distance definitions (smaller = closer):
+ *   COS  = 1 - a.b / (|a| |b|)     L2SQ = sum (a-b)^2  (no sqrt)     IP = 1 - a.b
+ * The reference never overrides the metric (usearch.rs:89-96 => crate default, cosine);
+ * the ABI makes it explicit. */
+typedef enum vs_metric { VS_METRIC_COS = 0, VS_METRIC_L2SQ = 1, VS_METRIC_IP = 2 } vs_metric;
+
+/* Mirrors IndexOptions built at usearch.rs:89-96 + reserve(RESERVE_INCREMENT) at :99.
+ * connectivity / expansion_add / expansion_search == 0 => library defaults 16 / 128 / 64
+ * (lib.rs:164,182,200: the newtypes default to 0). */
+typedef struct vs_options {
+    size_t dims;              /* Dimensions (lib.rs:147); must be > 0                       */
+    int32_t metric;           /* vs_metric                                                  */
+    size_t connectivity;      /* M: level-0 rows hold 2M links, upper levels M              */
+    size_t expansion_add;     /* ef used while inserting                                    */
+    size_t expansion_search;  /* default ef for vs_search (effective ef = max(ef, k))       */
+    size_t capacity_hint;     /* initial reserve; 0 => 1 000 000 (usearch.rs:62,99)         */
+    int32_t device;           /* CUDA device ordinal of this shard (one index = one GPU)    */
+    size_t max_batch;         /* insertion batch cap; 0 => library default                  */
+    uint64_t reserved[4];     /* must be zero                                               */
+} vs_options;
+
+/* Work counters; device-side counters are collected only when enabled with
+ * vs_set_stats(index, 1) (they cost atomics). */
+typedef struct vs_stats {
+    uint64_t count;              /* live vectors (adds - removes)                           */
+    uint64_t slots;              /* slots ever used (live + tombstoned)                     */
+    uint64_t capacity;
+    uint64_t pending;            /* staged adds not yet in the graph                        */
+    uint64_t search_queries;     /* since creation / last vs_reset_stats                    */
+    uint64_t search_dist_evals;
+    uint64_t search_expansions;  /* beam pops that fetched a neighbour row                  */
+    uint64_t build_vectors;
+    uint64_t build_dist_evals;
+    uint64_t build_batches;
+    double   build_seconds;      /* device time spent inside insertion batches              */
+    uint64_t device_bytes;       /* HBM held by this index                                  */
+    uint32_t top_level;
+    uint32_t reserved32;
+} vs_stats;
+
+/* usearch::Index::new + reserve — usearch.rs:82-99 (called from create_index, :38-53). */
+vs_status vs_index_create(const vs_options* options, vs_index** out);
+/* Dropping the last Sender<Index> ends the actor and frees the index — usearch.rs:120,133. */
+void vs_index_destroy(vs_index* index);
+
+/* usearch::Index::add(key, &embedding) — usearch.rs:221. Adding a key that is present
+ * replaces it (remove + add under the same key — usearch.rs:214-225). Adds are staged
+ * and land in the graph in batches; vs_count/vs_search/vs_flush make them land. */
+vs_status vs_add(vs_index* index, uint64_t key, const float* vec);
+vs_status vs_add_batch(vs_index* index, size_t n, const uint64_t* keys, const float* vecs /* n x dims, row-major */);
+/* Same, rows already resident in HBM on the index's device (keys stay on the host). */
+vs_status vs_add_batch_device(vs_index* index, size_t n, const uint64_t* keys, const float* d_vecs);
+
+/* usearch::Index::remove(key) — usearch.rs:215,245. Tombstone; count drops by one. */
+vs_status vs_remove(vs_index* index, uint64_t key);
+
+/* usearch::Index::search(&embedding, limit) -> Matches{keys, distances} — usearch.rs:276,288,298.
+ * Results ascending by (distance, key); *found <= k (fewer if the index is smaller).
+ * ef_override == 0 => expansion_search; exact != 0 => brute force over all live vectors.
+ * keys_out / dist_out hold nq x k entries; unused tail entries are UINT64_MAX / +inf. */
+vs_status vs_search(vs_index* index, const float* query, size_t k,
+                    uint64_t* keys_out, float* dist_out, size_t* found);
+vs_status vs_search_batch(vs_index* index, size_t nq, const float* queries, size_t k,
+                          size_t ef_override, int exact,
+                          uint64_t* keys_out, float* dist_out, size_t* found /* nq entries, may be NULL */);
+/* Device-resident variant: d_queries, d_keys_out, d_dist_out are device pointers on the
+ * index's device; enqueues on `stream` (a cudaStream_t, NULL = the index's own stream)
+ * and returns without synchronising when stream != NULL. */
+vs_status vs_search_batch_device(vs_index* index, size_t nq, const float* d_queries, size_t k,
+                                 size_t ef_override, int exact,
+                                 uint64_t* d_keys_out, float* d_dist_out, void* stream);
+
+/* usearch::Index::size / capacity / reserve — usearch.rs:201-206,309. */
+size_t vs_count(vs_index* index);
+size_t vs_capacity(vs_index* index);
+vs_status vs_reserve(vs_index* index, size_t capacity);
+
+/* New: force staged adds into the graph (the reference's tests poll count() instead —
+ * usearch.rs:352-358). */
+vs_status vs_flush(vs_index* index);
+
+vs_status vs_get_stats(vs_index* index, vs_stats* out);
+vs_status vs_set_stats(vs_index* index, int enabled);
+vs_status vs_reset_stats(vs_index* index);
+
+/* Sharded search: merge `parts` per-shard result lists
+ * (each nq x k, ascending) laid out [part][query][k] into the global top-k per query.
+ * Device pointers on `device`; runs on `stream`. Follows the NCCL all-gather. */
+vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k,
+                               const uint64_t* d_keys_in, const float* d_dist_in,
+                               uint64_t* d_keys_out, float* d_dist_out, void* stream);
+
+/* Debug/verification: copy the level-`level` neighbour table to the host.
+ * links_out holds n_rows x row_width u32 slot ids (UINT32_MAX = empty);
+ * slot_keys_out (may be NULL) holds the u64 key of each of the `slots` slots.
+ * Query the sizes first with links_out == NULL. */
+vs_status vs_export_level(vs_index* index, uint32_t level, uint32_t* links_out,
+                          size_t* n_rows, size_t* row_width, uint64_t* slot_keys_out, size_t* slots);
+
+/* Thread-local message of the last failing call on this thread. */
+const char* vs_last_error(void);
+/* "vsann-b200 <version> sm_100a" for the GPU library, "vsann-oracle ..." for the oracle. */
+const char* vs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSANN_H */

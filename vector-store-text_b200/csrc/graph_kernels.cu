@@ -1,0 +1,396 @@
+// graph_kernels.cu — K3 (ANN search), K4 (batched insertion: search + heuristic select) and
+// K5 (reverse-link merge / re-prune) for the fixed-degree neighbour tables.
+//
+// Reference behaviour restated: usearch::Index::search (src/index/usearch.rs:276) and
+// usearch::Index::add (src/index/usearch.rs:221); algorithm per SURVEY.md Appendix B, CPU
+// restatement in oracle/oracle_vsann.cpp (hnsw_search / hnsw_insert / select_heuristic).
+#include "beam.cuh"
+#include "kernels.h"
+
+namespace vsann {
+
+__device__ __forceinline__ float warp_sqnorm(const float4* q4, int chunks) {
+    float acc = 0.f;
+    for (int c = lane_id(); c < chunks; c += 32) { const float4 v = q4[c]; acc = fmaf(v.x, v.x, acc); acc = fmaf(v.y, v.y, acc); acc = fmaf(v.z, v.z, acc); acc = fmaf(v.w, v.w, acc); }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    return acc;
+}
+
+// Loads a query given with `dims` floats (row stride `ld`) into the padded shared buffer.
+__device__ __forceinline__ void warp_load_query(float4* q4, const float* q, uint32_t dims, uint32_t dpad) {
+    float* qs = reinterpret_cast<float*>(q4);
+    for (uint32_t i = lane_id(); i < dpad; i += 32) qs[i] = i < dims ? q[i] : 0.f;
+    __syncwarp();
+}
+
+// ---------------------------------------------------------------- K3: ANN search ------------
+__global__ void __launch_bounds__(128) k_search(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+                                                uint32_t ef, uint32_t efp, uint32_t hsize,
+                                                uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
+                                                unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, efp, hsize);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, ef, efp, hsize);
+    uint32_t evals = 0, exps = 0, done = 0;
+    for (uint32_t q = blockIdx.x * wpb + warp; q < nq; q += gridDim.x * wpb) {
+        warp_load_query(S.q4, queries + (size_t)q * g.dims, g.dims, g.dpad);
+        uint64_t* ko = keys_out + (size_t)q * k; float* dd = dist_out + (size_t)q * k;
+        uint32_t nout = 0;
+        if (g.n_slots > 0) {
+            const float qn = g.metric == COS ? warp_sqnorm(S.q4, g.chunks) : 0.f;
+            uint32_t cur = 0; float dcur = warp_entry_dist(g, S, qn, 0u, evals);
+            for (int l = g.top_level; l >= 1; --l) greedy_level(g, l, S, qn, cur, dcur, evals, exps);
+            beam_seed(S, cur, dcur);
+            beam_level(g, 0, S, qn, evals, exps);
+            // emit the first k live entries
+            for (int base = 0; base < (int)ef && nout < k; base += 32) {
+                const int i = base + lane;
+                uint32_t id = i < (int)ef ? S.L.li[i] : NONE;
+                const float d = i < (int)ef ? S.L.ld[i] : INFINITY;
+                bool live = false;
+                if (id != NONE) { id &= ~EXPANDED; live = !is_deleted(g, id); }
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
+                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = d; }
+                nout += __popc(m);
+            }
+            if (nout > k) nout = k;
+        }
+        for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
+        ++done;
+        __syncwarp();
+    }
+    if (counters && lane == 0) {
+        atomicAdd(&counters[0], (unsigned long long)done);
+        atomicAdd(&counters[1], (unsigned long long)evals);
+        atomicAdd(&counters[2], (unsigned long long)exps);
+    }
+}
+
+// ------------------------------------------------- K4a: insertion search on the frozen graph --
+// One warp per batch item: greedy descent from the top, then an ef_add beam on every level the
+// item lives on; each level's sorted candidate list goes to scratch (cand_id / cand_d).
+// Level-l lists of the items with slot % M^l == 0 are stored at item index (slot/M^l - first_row[l]).
+__global__ void __launch_bounds__(128) k_build_search(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize,
+                                                      unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, efp, hsize);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, ef, efp, hsize);
+    uint32_t evals = 0, exps = 0;
+    for (uint32_t it = blockIdx.x * wpb + warp; it < b.count; it += gridDim.x * wpb) {
+        const uint32_t slot = b.first_slot + it;
+        int lvl = 0;
+        while (lvl + 1 <= b.new_top && slot % g.stride[lvl + 1] == 0) ++lvl;
+        // mark "no candidates" for every level first
+        for (int l = 0; l <= lvl; ++l) {
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            if (lane == 0) b.cand_n[l][idx] = 0;
+        }
+        if (g.n_slots == 0) continue;
+        const float qn = warp_load_row(g, S.q4, slot);
+        uint32_t cur = 0; float dcur = warp_entry_dist(g, S, qn, 0u, evals);
+        for (int l = g.top_level; l > lvl; --l) greedy_level(g, l, S, qn, cur, dcur, evals, exps);
+        beam_seed(S, cur, dcur);
+        for (int l = min(lvl, g.top_level); l >= 0; --l) {
+            beam_level(g, l, S, qn, evals, exps);
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
+            uint32_t n = 0;
+            for (int i = lane; i < (int)efp; i += 32) {
+                const uint32_t id = S.L.li[i];
+                ci[i] = id == NONE ? NONE : (id & ~EXPANDED); cd[i] = S.L.ld[i];
+                n += (id != NONE);
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+            if (lane == 0) b.cand_n[l][idx] = n;
+            if (l > 0) beam_reseed_from_list(S);
+        }
+    }
+    if (counters && lane == 0) { atomicAdd(&counters[3], (unsigned long long)evals); atomicAdd(&counters[4], (unsigned long long)exps); }
+}
+
+// ------------------------------------------------- heuristic selection (shared by K4b / K5) ---
+// Candidates arrive ascending by distance to the base through next(); a candidate is kept iff
+// it is at least as close to the base as to every neighbour kept so far. The kept ids live one
+// per lane. Uses S.q4 as the staging buffer for the candidate row.
+struct KeepSet { uint32_t id; int n; };   // lane j < n holds kept id j
+
+__device__ __forceinline__ bool heuristic_try(const GraphView& g, WarpSmem& S, KeepSet& K, uint32_t c, float d_base, uint32_t& evals) {
+    bool good = true;
+    if (K.n > 0) {
+        const float cn = warp_load_row(g, S.q4, c);
+        const float dk = warp_dist32(g, S.q4, cn, (int)lane_id() < K.n ? K.id : NONE, S.scr_id, S.scr_d, evals);
+        good = __ballot_sync(0xffffffffu, dk < d_base) == 0u;
+    }
+    if (good) { if ((int)lane_id() == K.n) K.id = c; ++K.n; }
+    return good;
+}
+
+// ------------------------------------------------- K4b: forward links + reverse-edge inbox ----
+// One warp per (item, level). Merges the graph candidates with the intra-batch kNN candidates
+// (both ascending), runs the heuristic with cap M, writes the item's row, and registers each
+// reverse edge (kept -> item) with the inbox of the kept node's row.
+__global__ void __launch_bounds__(128) k_select(GraphView g, BuildBatch b, LinkTables t, uint32_t efp, uint32_t kbp,
+                                                unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, 32, 32);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 32, 32, 32);
+    uint32_t evals = 0;
+    for (uint32_t w = blockIdx.x * wpb + warp; w < b.total_items; w += gridDim.x * wpb) {
+        int l = 0; while (l + 1 <= b.new_top && w >= b.item_off[l + 1]) ++l;
+        const uint32_t idx = w - b.item_off[l];
+        const uint32_t slot = (b.first_row[l] + idx) * g.stride[l];
+        const uint32_t* gi = b.cand_id[l] + (size_t)idx * efp; const float* gd = b.cand_d[l] + (size_t)idx * efp;
+        const uint32_t* bi = b.knn_id[l] + (size_t)idx * kbp; const float* bd = b.knn_d[l] + (size_t)idx * kbp;
+        const uint32_t gn = b.cand_n[l][idx];
+        uint32_t bn = 0;
+        if (b.knn_id[l]) { for (uint32_t i = lane; i < kbp; i += 32) bn += (bi[i] != NONE); for (int o = 16; o >= 1; o >>= 1) bn += __shfl_xor_sync(0xffffffffu, bn, o); }
+        KeepSet K{NONE, 0};
+        uint32_t a = 0, c = 0;
+        const int cap = (int)g.M;
+        while (K.n < cap && (a < gn || c < bn)) {
+            uint32_t id; float d;
+            const bool take_g = a < gn && (c >= bn || pair_less(gd[a], gi[a], bd[c], bi[c]));
+            if (take_g) { id = gi[a]; d = gd[a]; ++a; } else { id = bi[c]; d = bd[c]; ++c; }
+            if (id == slot) continue;
+            heuristic_try(g, S, K, id, d, evals);
+        }
+        // forward row
+        int width; uint32_t* row = const_cast<uint32_t*>(level_row(g, l, slot, width));
+        for (int i = lane; i < width; i += 32) row[i] = NONE;
+        __syncwarp();
+        if ((int)lane < K.n) {
+            row[lane] = K.id;
+            // reverse edge: K.id <- slot
+            const uint32_t r = t.row_base[l] + K.id / g.stride[l];
+            const uint32_t e = atomicAdd(t.n_edges, 1u);
+            t.edge_row[e] = r; t.edge_src[e] = slot;
+            if (atomicAdd(&t.inbox_cnt[r], 1u) == 0u) {
+                const uint32_t ti = atomicAdd(t.n_touched, 1u);
+                t.touched_row[ti] = r; t.touched_slot[ti] = K.id; t.touched_level[ti] = (uint8_t)l;
+                t.inbox_idx[r] = ti;
+            }
+        }
+        __syncwarp();
+    }
+    if (counters && lane == 0) atomicAdd(&counters[3], (unsigned long long)evals);
+}
+
+__global__ void k_inbox_fill(LinkTables t) {
+    const uint32_t n = *t.n_edges;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t ti = t.inbox_idx[t.edge_row[e]];
+        const uint32_t pos = atomicAdd(&t.inbox_fill[ti], 1u);
+        if (pos < INBOX_CAP) t.inbox[(size_t)ti * INBOX_CAP + pos] = t.edge_src[e];
+    }
+}
+
+// ------------------------------------------------- K5: reverse-link merge / re-prune ----------
+// One warp per touched row: candidates = current row + inbox; if they fit the row they are
+// appended (sorted by distance), otherwise the heuristic re-prunes to the row cap.
+__global__ void __launch_bounds__(128) k_reverse_merge(GraphView g, LinkTables t, unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, 64, 32);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 64, 64, 32);
+    const uint32_t ntouched = *t.n_touched;
+    uint32_t evals = 0;
+    for (uint32_t w = blockIdx.x * wpb + warp; w < ntouched; w += gridDim.x * wpb) {
+        const uint32_t v = t.touched_slot[w]; const int l = t.touched_level[w]; const uint32_t r = t.touched_row[w];
+        int width; uint32_t* row = const_cast<uint32_t*>(level_row(g, l, v, width));
+        const float vn = warp_load_row(g, S.q4, v);
+        slist_init(S.L);
+        uint32_t total = 0;
+        {   // existing links
+            uint32_t id = (int)lane < width ? row[lane] : NONE;
+            total += __popc(__ballot_sync(0xffffffffu, id != NONE));
+            const float d = warp_dist32(g, S.q4, vn, id, S.scr_id, S.scr_d, evals);
+            slist_merge(S.L, d, id, S.scr_id, S.scr_d);
+        }
+        {   // inbox
+            const uint32_t nin = min(t.inbox_fill[w], (uint32_t)INBOX_CAP);
+            uint32_t id = lane < nin ? t.inbox[(size_t)w * INBOX_CAP + lane] : NONE;
+            if (id == v) id = NONE;
+            const float d = warp_dist32(g, S.q4, vn, id, S.scr_id, S.scr_d, evals);
+            slist_merge(S.L, d, id, S.scr_id, S.scr_d);
+        }
+        // count distinct candidates now in the list
+        uint32_t n = 0;
+        for (int i = lane; i < 64; i += 32) n += (S.L.li[i] != NONE);
+        for (int o = 16; o >= 1; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+        if ((int)n <= width) {
+            for (int i = lane; i < width; i += 32) row[i] = i < (int)n ? S.L.li[i] : NONE;
+        } else {
+            KeepSet K{NONE, 0};
+            for (uint32_t i = 0; i < n && K.n < width; ++i) heuristic_try(g, S, K, S.L.li[i], S.L.ld[i], evals);
+            // heuristic_try clobbers S.q4 (candidate row staging); the list survives in S.L
+            for (int i = lane; i < width; i += 32) row[i] = NONE;
+            __syncwarp();
+            if ((int)lane < K.n) row[lane] = K.id;
+        }
+        if (lane == 0) { t.inbox_cnt[r] = 0; t.inbox_fill[w] = 0; }
+        __syncwarp();
+    }
+    if (counters && lane == 0) atomicAdd(&counters[3], (unsigned long long)evals);
+}
+
+// ------------------------------------------------- small utility kernels ----------------------
+__global__ void k_row_norms(const float* __restrict__ vecs, float* __restrict__ sqn, uint32_t first, uint32_t n, uint32_t dpad) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* v = vecs + (size_t)(first + i) * dpad;
+    float acc = 0.f;
+    for (uint32_t c = 0; c < dpad; ++c) acc = fmaf(v[c], v[c], acc);   // sequential chain = oracle's dot_seq(v, v)
+    sqn[first + i] = acc;
+}
+
+// src rows (dims floats, dense) -> padded table rows
+__global__ void k_scatter_rows(const float* __restrict__ src, float* __restrict__ vecs, uint32_t first, uint32_t n, uint32_t dims, uint32_t dpad) {
+    const size_t total = (size_t)n * dpad;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t r = (uint32_t)(i / dpad), c = (uint32_t)(i % dpad);
+        vecs[(size_t)(first + r) * dpad + c] = c < dims ? src[(size_t)r * dims + c] : 0.f;
+    }
+}
+
+__global__ void k_tombstone(uint32_t* deleted, const uint32_t* __restrict__ slots, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) atomicOr(&deleted[slots[i] >> 5], 1u << (slots[i] & 31u));
+}
+
+// ------------------------------------------------- K6: sharded top-k merge --------------------
+// One warp per query; `parts` ascending lists of k (dist, key) each -> global top-k by (dist, key).
+__global__ void k_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* __restrict__ keys_in, const float* __restrict__ dist_in,
+                             uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
+    const uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = lane_id();
+    if (q >= nq) return;
+    // lane p (< 32) owns the head pointer of parts p, p+32, ...; k-step tournament
+    uint32_t head[4] = {0, 0, 0, 0};   // supports up to 128 parts
+    for (uint32_t o = 0; o < k; ++o) {
+        float bd = INFINITY; uint64_t bk = 0xFFFFFFFFFFFFFFFFull; uint32_t bp = NONE;
+        for (uint32_t j = 0, p = lane; p < parts && j < 4; ++j, p += 32) {
+            if (head[j] < k) {
+                const size_t off = ((size_t)p * nq + q) * k + head[j];
+                const float d = dist_in[off]; const uint64_t key = keys_in[off];
+                if (d < bd || (d == bd && key < bk)) { bd = d; bk = key; bp = p; }
+            }
+        }
+        float wd = bd; uint64_t wk = bk; uint32_t wp = bp;
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, wd, s);
+            const uint64_t ok = __shfl_xor_sync(0xffffffffu, wk, s);
+            const uint32_t op = __shfl_xor_sync(0xffffffffu, wp, s);
+            if (od < wd || (od == wd && (ok < wk || (ok == wk && op < wp)))) { wd = od; wk = ok; wp = op; }
+        }
+        if (lane == 0) { keys_out[(size_t)q * k + o] = wk; dist_out[(size_t)q * k + o] = wd; }
+        if (wp != NONE && (wp & 31u) == lane) ++head[wp >> 5];
+    }
+}
+
+// ------------------------------------------------- launchers ----------------------------------
+static inline uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
+
+static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t smem_limit, uint32_t hash_factor) {
+    SearchPlan p;
+    p.efp = (ef + 31u) & ~31u;
+    uint32_t hs = next_pow2(ef * hash_factor);
+    if (hs < 1024) hs = 1024;
+    if (hs > 16384) hs = 16384;
+    size_t per_warp = warp_smem_bytes(dpad, p.efp, hs);
+    while (per_warp > smem_limit && hs > 256) { hs >>= 1; per_warp = warp_smem_bytes(dpad, p.efp, hs); }
+    p.hsize = hs;
+    uint32_t wpb = 4;
+    while (wpb > 1 && per_warp * wpb > smem_limit / 2) wpb >>= 1;
+    p.warps_per_block = wpb;
+    p.smem = per_warp * wpb;
+    p.blocks_per_sm = (uint32_t)(smem_limit / (p.smem + 1024));
+    if (p.blocks_per_sm < 1) p.blocks_per_sm = 1;
+    if (p.blocks_per_sm * wpb > 48) p.blocks_per_sm = 48 / wpb;
+    (void)sm_count;
+    return p;
+}
+
+cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    if (nq == 0) return cudaSuccess;
+    const SearchPlan p = plan_search(g.dpad, ef, dev.sm_count, dev.smem_per_block, dev.hash_factor);
+    if (p.smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+    if (e != cudaSuccess) return e;
+    uint32_t blocks = (nq + p.warps_per_block - 1) / p.warps_per_block;
+    const uint32_t maxb = dev.sm_count * p.blocks_per_sm;
+    if (blocks > maxb) blocks = maxb;
+    k_search<<<blocks, p.warps_per_block * 32, p.smem, st>>>(g, d_queries, nq, k, ef, p.efp, p.hsize, d_keys, d_dist, counters);
+    return cudaGetLastError();
+}
+
+uint32_t build_efp(uint32_t ef) { return (ef + 31u) & ~31u; }
+
+cudaError_t launch_build_search(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
+                                unsigned long long* counters, cudaStream_t st) {
+    const SearchPlan p = plan_search(g.dpad, ef, dev.sm_count, dev.smem_per_block, dev.hash_factor);
+    if (p.smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_build_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+    if (e != cudaSuccess) return e;
+    uint32_t blocks = (b.count + p.warps_per_block - 1) / p.warps_per_block;
+    const uint32_t maxb = dev.sm_count * p.blocks_per_sm;
+    if (blocks > maxb) blocks = maxb;
+    if (blocks == 0) return cudaSuccess;
+    k_build_search<<<blocks, p.warps_per_block * 32, p.smem, st>>>(g, b, ef, p.efp, p.hsize, counters);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_link(const GraphView& g, const BuildBatch& b, const LinkTables& t, uint32_t efp, uint32_t kbp, const DeviceInfo& dev,
+                        unsigned long long* counters, cudaStream_t st) {
+    if (b.total_items == 0) return cudaSuccess;
+    const uint32_t wpb = 4;
+    size_t smem = warp_smem_bytes(g.dpad, 32, 32) * wpb;
+    cudaError_t e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    uint32_t blocks = (b.total_items + wpb - 1) / wpb;
+    uint32_t maxb = dev.sm_count * 8; if (blocks > maxb) blocks = maxb;
+    k_select<<<blocks, wpb * 32, smem, st>>>(g, b, t, efp, kbp, counters);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    k_inbox_fill<<<dev.sm_count * 4, 256, 0, st>>>(t);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    smem = warp_smem_bytes(g.dpad, 64, 32) * wpb;
+    e = cudaFuncSetAttribute(k_reverse_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    // touched rows <= reverse edges <= total_items * M (device-side count bounds the loop)
+    uint64_t maxw = (uint64_t)b.total_items * g.M;
+    blocks = (uint32_t)((maxw + wpb - 1) / wpb); if (blocks > maxb) blocks = maxb;
+    k_reverse_merge<<<blocks, wpb * 32, smem, st>>>(g, t, counters);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_row_prepare(const float* d_src, float* vecs, float* sqn, uint32_t first, uint32_t n, uint32_t dims, uint32_t dpad, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const size_t total = (size_t)n * dpad;
+    uint32_t blocks = (uint32_t)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
+    k_scatter_rows<<<blocks, 256, 0, st>>>(d_src, vecs, first, n, dims, dpad);
+    k_row_norms<<<(n + 127) / 128, 128, 0, st>>>(vecs, sqn, first, n, dpad);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tombstone(uint32_t* deleted, const uint32_t* d_slots, uint32_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_tombstone<<<(n + 255) / 256, 256, 0, st>>>(deleted, d_slots, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* keys_in, const float* dist_in,
+                              uint64_t* keys_out, float* dist_out, cudaStream_t st) {
+    if (nq == 0 || k == 0) return cudaSuccess;
+    if (parts > 128) return cudaErrorInvalidValue;
+    const uint32_t threads = 128, qpb = threads / 32;
+    k_merge_topk<<<(nq + qpb - 1) / qpb, threads, 0, st>>>(parts, nq, k, keys_in, dist_in, keys_out, dist_out);
+    return cudaGetLastError();
+}
+
+}  // namespace vsann

@@ -1,0 +1,519 @@
+// index.cu — host side of libvsann.so: the C ABI of include/vsann.h over the sm_100a kernels.
+//
+// Mirrors what the reference's index actor does around usearch (src/index/usearch.rs):
+//   new + reserve           usearch.rs:82-99      -> vs_index_create
+//   add / replace           usearch.rs:174-233    -> vs_add*, staged and landed in batches
+//   remove (tombstone)      usearch.rs:235-249    -> vs_remove
+//   search -> Matches       usearch.rs:251-306    -> vs_search*
+//   size / capacity/reserve usearch.rs:201-212,308-311 -> vs_count / vs_capacity / vs_reserve
+// There is no CPU path in this library: every operation that touches vectors runs on the GPU.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/vsann.h"
+#include "kernels.h"
+
+using namespace vsann;
+
+namespace vsann {
+__global__ void k_pad(const float* __restrict__ src, float* __restrict__ dst, uint32_t n, uint32_t dims, uint32_t dpad) {
+    const size_t total = (size_t)n * dpad;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t r = (uint32_t)(i / dpad), c = (uint32_t)(i % dpad);
+        dst[i] = c < dims ? src[(size_t)r * dims + c] : 0.f;
+    }
+}
+}
+static cudaError_t pad_queries(const float* src, float* dst, uint32_t n, uint32_t dims, uint32_t dpad, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const size_t total = (size_t)n * dpad;
+    uint32_t blocks = (uint32_t)std::min<size_t>((total + 255) / 256, 148 * 8);
+    vsann::k_pad<<<blocks, 256, 0, st>>>(src, dst, n, dims, dpad);
+    return cudaGetLastError();
+}
+
+namespace {
+thread_local std::string g_err;
+vs_status fail(vs_status s, const std::string& m) { g_err = m; return s; }
+#define CU(expr)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) return fail(VS_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+template <class T> struct DBuf {
+    T* p = nullptr; size_t n = 0;
+    cudaError_t ensure(size_t want) {
+        if (want <= n) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) n = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+}  // namespace
+
+struct vs_index {
+    // options
+    uint32_t dims = 0, dpad = 0; int metric = 0; uint32_t M = 16, W0 = 32, efA = 128, efS = 64;
+    uint32_t max_batch = 16384; size_t reserve_increment = 1000000;
+    DeviceInfo dev; cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, user_ev = nullptr; bool user_pending = false;
+    std::mutex mu;
+    // tables
+    size_t capacity = 0; uint32_t n_slots = 0; size_t live = 0; int top_level = 0; int n_levels = 1;
+    float* vecs = nullptr; float* sqn = nullptr; uint32_t* links0 = nullptr; uint32_t* linksU[MAX_LEVELS] = {};
+    uint64_t* slot_key = nullptr; uint32_t* deleted = nullptr;
+    uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
+    LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
+    // build scratch
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, stage;
+    DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
+    unsigned long long* counters = nullptr; bool stats_on = false;
+    // host state
+    std::unordered_map<uint64_t, uint32_t> key_slot;
+    std::vector<uint64_t> pend_keys; std::vector<float> pend_vecs; std::unordered_map<uint64_t, size_t> pend_pos;
+    std::vector<uint64_t> host_slot_key;
+    uint64_t st_build_vectors = 0, st_build_batches = 0; double st_build_seconds = 0; size_t device_bytes = 0;
+
+    GraphView view(uint32_t visible, int top) const {
+        GraphView g{};
+        g.vecs = vecs; g.sqn = sqn; g.links0 = links0;
+        for (int l = 0; l < MAX_LEVELS; ++l) { g.linksU[l] = linksU[l]; g.stride[l] = stride[l] ? stride[l] : 0xFFFFFFFFu; }
+        g.deleted = deleted; g.slot_key = slot_key; g.n_slots = visible;
+        g.dims = dims; g.dpad = dpad; g.chunks = dpad / 4; g.M = M; g.W0 = W0; g.metric = metric; g.top_level = top;
+        return g;
+    }
+};
+
+namespace {
+
+int top_for(const vs_index* ix, uint32_t n) {
+    int t = 0;
+    for (int l = 1; l < ix->n_levels; ++l) if (n > 0 && ix->stride[l] <= n - 1) t = l;
+    return t;
+}
+
+template <class T> cudaError_t grow(T*& p, size_t old_n, size_t new_n, int fill_byte, cudaStream_t st, size_t& bytes) {
+    T* np = nullptr;
+    cudaError_t e = cudaMalloc(&np, new_n * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (fill_byte >= 0) { e = cudaMemsetAsync(np, fill_byte, new_n * sizeof(T), st); if (e != cudaSuccess) { cudaFree(np); return e; } }
+    if (p && old_n) { e = cudaMemcpyAsync(np, p, std::min(old_n, new_n) * sizeof(T), cudaMemcpyDeviceToDevice, st); if (e != cudaSuccess) { cudaFree(np); return e; } }
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { cudaFree(np); return e; }
+    if (p) cudaFree(p);
+    bytes += (new_n - (p ? old_n : 0)) * sizeof(T);
+    p = np;
+    return cudaSuccess;
+}
+
+// usearch::Index::reserve (usearch.rs:99,206): grows every table; contents are preserved.
+vs_status do_reserve(vs_index* ix, size_t cap) {
+    if (cap <= ix->capacity) return VS_OK;
+    if (cap >= 0x7FFFFFF0ull) return fail(VS_ERR_CAPACITY, "reserve: capacity exceeds 2^31 slots per shard");
+    cudaSetDevice(ix->dev.device);
+    const size_t old = ix->capacity;
+    cudaError_t e;
+#define GROW(call) do { e = (call); if (e != cudaSuccess) { cudaGetLastError(); return fail(VS_ERR_CAPACITY, std::string("reserve: ") + cudaGetErrorString(e)); } } while (0)
+    GROW(grow(ix->vecs, old * ix->dpad, cap * ix->dpad, -1, ix->stream, ix->device_bytes));
+    GROW(grow(ix->sqn, old, cap, -1, ix->stream, ix->device_bytes));
+    GROW(grow(ix->links0, old * ix->W0, cap * ix->W0, 0xFF, ix->stream, ix->device_bytes));
+    GROW(grow(ix->slot_key, old, cap, 0xFF, ix->stream, ix->device_bytes));
+    GROW(grow(ix->deleted, (old + 31) / 32, (cap + 31) / 32, 0, ix->stream, ix->device_bytes));
+    // level tables: level l exists while M^l < capacity
+    int nl = 1; uint64_t s = ix->M;
+    while (nl < MAX_LEVELS && s < cap) { ix->stride[nl] = (uint32_t)s; ++nl; s *= ix->M; }
+    ix->stride[0] = 1;
+    size_t total = cap; ix->lt.row_base[0] = 0;
+    for (int l = 1; l < nl; ++l) {
+        const size_t nr = (cap + ix->stride[l] - 1) / ix->stride[l];
+        GROW(grow(ix->linksU[l], ix->rows[l] * ix->M, nr * ix->M, 0xFF, ix->stream, ix->device_bytes));
+        ix->rows[l] = nr; ix->lt.row_base[l] = (uint32_t)total; total += nr;
+    }
+    ix->rows[0] = cap; ix->n_levels = nl;
+    // inbox index space covers all rows; it is all-zero between batches so no copy is needed
+    if (ix->lt.inbox_cnt) { cudaFree(ix->lt.inbox_cnt); cudaFree(ix->lt.inbox_idx); ix->device_bytes -= ix->total_rows * 8; ix->lt.inbox_cnt = ix->lt.inbox_idx = nullptr; }
+    GROW(cudaMalloc(&ix->lt.inbox_cnt, total * 4)); GROW(cudaMalloc(&ix->lt.inbox_idx, total * 4));
+    GROW(cudaMemsetAsync(ix->lt.inbox_cnt, 0, total * 4, ix->stream)); GROW(cudaMemsetAsync(ix->lt.inbox_idx, 0xFF, total * 4, ix->stream));
+    GROW(cudaStreamSynchronize(ix->stream));
+    ix->total_rows = total; ix->device_bytes += total * 8;
+#undef GROW
+    ix->capacity = cap;
+    ix->host_slot_key.resize(cap);
+    return VS_OK;
+}
+
+// Carves the per-batch scratch (candidate lists, intra-batch neighbours, edge/inbox arrays).
+vs_status setup_build_scratch(vs_index* ix) {
+    const uint32_t B = ix->max_batch, efp = build_efp(ix->efA), kbp = KNN_BATCH;
+    ix->efpA = efp;
+    size_t bytes = 0; size_t off_ci[MAX_LEVELS], off_cd[MAX_LEVELS], off_cn[MAX_LEVELS], off_ki[MAX_LEVELS], off_kd[MAX_LEVELS];
+    auto take = [&](size_t b) { size_t o = bytes; bytes += (b + 255) & ~(size_t)255; return o; };
+    size_t items_total = 0; uint64_t s = 1;
+    for (int l = 0; l < MAX_LEVELS; ++l) {
+        const size_t it = B / s + 2; items_total += it;
+        off_ci[l] = take(it * efp * 4); off_cd[l] = take(it * efp * 4); off_cn[l] = take(it * 4);
+        off_ki[l] = take(it * kbp * 4); off_kd[l] = take(it * kbp * 4);
+        s *= ix->M; if (s > 0xFFFFFFFFull) s = 0xFFFFFFFFull;
+    }
+    ix->edge_cap = items_total * ix->M;
+    const size_t ec = ix->edge_cap;
+    const size_t o_ne = take(8), o_er = take(ec * 4), o_es = take(ec * 4), o_tr = take(ec * 4), o_ts = take(ec * 4), o_tl = take(ec),
+                 o_if = take(ec * 4), o_in = take(ec * INBOX_CAP * 4);
+    CU(ix->build_scratch.ensure(bytes));
+    unsigned char* p = ix->build_scratch.p;
+    CU(cudaMemsetAsync(p, 0, bytes, ix->stream));
+    for (int l = 0; l < MAX_LEVELS; ++l) {
+        ix->bb.cand_id[l] = (uint32_t*)(p + off_ci[l]); ix->bb.cand_d[l] = (float*)(p + off_cd[l]); ix->bb.cand_n[l] = (uint32_t*)(p + off_cn[l]);
+        ix->bb.knn_id[l] = (uint32_t*)(p + off_ki[l]); ix->bb.knn_d[l] = (float*)(p + off_kd[l]);
+    }
+    ix->lt.n_edges = (uint32_t*)(p + o_ne); ix->lt.n_touched = ix->lt.n_edges + 1;
+    ix->lt.edge_row = (uint32_t*)(p + o_er); ix->lt.edge_src = (uint32_t*)(p + o_es);
+    ix->lt.touched_row = (uint32_t*)(p + o_tr); ix->lt.touched_slot = (uint32_t*)(p + o_ts); ix->lt.touched_level = (uint8_t*)(p + o_tl);
+    ix->lt.inbox_fill = (uint32_t*)(p + o_if); ix->lt.inbox = (uint32_t*)(p + o_in);
+    CU(ix->exact_scratch.ensure(exact_scratch_bytes(B, KNN_BATCH, ix->dev.sm_count)));
+    return VS_OK;
+}
+
+// K4 + K5 for slots [first, first + count): search on the frozen graph, intra-batch exact
+// neighbours, heuristic selection, reverse-link merge.
+vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
+    BuildBatch b = ix->bb;   // scratch pointers
+    b.first_slot = first; b.count = count;
+    b.new_top = top_for(ix, first + count);
+    uint32_t off = 0;
+    uint32_t* knn_id_saved[MAX_LEVELS]; float* knn_d_saved[MAX_LEVELS];
+    for (int l = 0; l < MAX_LEVELS; ++l) {
+        knn_id_saved[l] = b.knn_id[l]; knn_d_saved[l] = b.knn_d[l];
+        b.item_off[l] = off;
+        if (l <= b.new_top) {
+            const uint32_t s = ix->stride[l];
+            const uint32_t fr = (first + s - 1) / s, lr = (first + count - 1) / s;
+            b.first_row[l] = fr; b.items[l] = lr >= fr ? lr - fr + 1 : 0;
+        } else { b.first_row[l] = 0; b.items[l] = 0; }
+        off += b.items[l];
+    }
+    b.item_off[MAX_LEVELS] = off; b.total_items = off;
+    unsigned long long* ctr = ix->stats_on ? ix->counters : nullptr;
+    GraphView frozen = ix->view(first, b.new_top);
+    CU(launch_build_search(frozen, b, ix->efA, ix->dev, ctr, ix->stream));
+    for (int l = 0; l <= b.new_top; ++l) {
+        if (b.items[l] < 2) { b.knn_id[l] = nullptr; b.knn_d[l] = nullptr; continue; }
+        const uint32_t s = ix->stride[l], fs = b.first_row[l] * s;
+        ExactCorpus c{}; c.vecs = ix->vecs + (size_t)fs * ix->dpad; c.sqn = ix->sqn + fs; c.row_stride = (size_t)s * ix->dpad; c.row_step = s;
+        c.first_slot = fs; c.n = b.items[l]; c.deleted = nullptr; c.slot_key = nullptr; c.n_slots = first + count;
+        ExactQueries q{}; q.q = c.vecs; q.stride = c.row_stride; q.nq = b.items[l]; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = fs; q.self_step = s;
+        const uint32_t k = std::min<uint32_t>(KNN_BATCH, b.items[l] - 1);
+        ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
+        CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ix->stream));
+    }
+    CU(cudaMemsetAsync(ix->lt.n_edges, 0, 8, ix->stream));
+    GraphView linked = ix->view(first + count, b.new_top);
+    CU(launch_link(linked, b, ix->lt, ix->efpA, KNN_BATCH, ix->dev, ctr, ix->stream));
+    ix->st_build_batches++;
+    return VS_OK;
+}
+
+// Lands every staged add: replace = tombstone the old slot + append a new one (usearch.rs:214-225).
+vs_status flush_locked(vs_index* ix, const float* d_rows /* device rows or null => pend_vecs */, size_t n_dev, const uint64_t* dev_keys) {
+    const bool from_dev = d_rows != nullptr;
+    const size_t n = from_dev ? n_dev : ix->pend_keys.size();
+    if (n == 0) return VS_OK;
+    cudaSetDevice(ix->dev.device);
+    const uint64_t* keys = from_dev ? dev_keys : ix->pend_keys.data();
+    // capacity growth: the reference's threshold / increment rule (usearch.rs:62-66,201-212)
+    while (ix->capacity - ix->n_slots < std::max(ix->reserve_increment / 3, n)) {
+        vs_status s = do_reserve(ix, ix->capacity + std::max(ix->reserve_increment, n)); if (s != VS_OK) return s;
+    }
+    const uint32_t base = ix->n_slots;
+    std::vector<uint32_t> dead;
+    for (size_t i = 0; i < n; ++i) {
+        const uint32_t slot = base + (uint32_t)i;
+        auto it = ix->key_slot.find(keys[i]);
+        if (it != ix->key_slot.end()) { dead.push_back(it->second); it->second = slot; ix->live--; }
+        else ix->key_slot.emplace(keys[i], slot);
+        ix->host_slot_key[slot] = keys[i];
+    }
+    if (!dead.empty()) {
+        CU(ix->tomb.ensure(dead.size()));
+        CU(cudaMemcpyAsync(ix->tomb.p, dead.data(), dead.size() * 4, cudaMemcpyHostToDevice, ix->stream));
+        CU(launch_tombstone(ix->deleted, ix->tomb.p, (uint32_t)dead.size(), ix->stream));
+    }
+    CU(cudaMemcpyAsync(ix->slot_key + base, keys, n * 8, cudaMemcpyHostToDevice, ix->stream));
+    if (!from_dev) {
+        CU(ix->stage.ensure(n * ix->dims * 4));
+        CU(cudaMemcpyAsync(ix->stage.p, ix->pend_vecs.data(), n * ix->dims * 4, cudaMemcpyHostToDevice, ix->stream));
+        d_rows = (const float*)ix->stage.p;
+    }
+    CU(launch_row_prepare(d_rows, ix->vecs, ix->sqn, base, (uint32_t)n, ix->dims, ix->dpad, ix->stream));
+    CU(cudaEventRecord(ix->ev0, ix->stream));
+    size_t done = 0;
+    while (done < n) {
+        const uint32_t cur = base + (uint32_t)done;
+        uint32_t bsz = cur == 0 ? 1024u : cur;                 // bootstrap block, then at most doubling
+        bsz = (uint32_t)std::min<size_t>({(size_t)bsz, (size_t)ix->max_batch, n - done});
+        vs_status s = insert_batch(ix, cur, bsz); if (s != VS_OK) return s;
+        done += bsz;
+    }
+    CU(cudaEventRecord(ix->ev1, ix->stream));
+    CU(cudaStreamSynchronize(ix->stream));
+    float ms = 0; cudaEventElapsedTime(&ms, ix->ev0, ix->ev1); ix->st_build_seconds += ms * 1e-3;
+    ix->n_slots = base + (uint32_t)n; ix->live += n; ix->top_level = top_for(ix, ix->n_slots);
+    ix->st_build_vectors += n;
+    if (!from_dev) { ix->pend_keys.clear(); ix->pend_vecs.clear(); ix->pend_pos.clear(); }
+    return VS_OK;
+}
+
+vs_status wait_user(vs_index* ix, cudaStream_t st) {
+    if (ix->user_pending) { CU(cudaStreamWaitEvent(st, ix->user_ev, 0)); }
+    return VS_OK;
+}
+
+// Search with device-resident queries/outputs on stream st (already ordered after the build).
+vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t k, size_t ef, int exact,
+                               uint64_t* d_keys, float* d_dist, cudaStream_t st) {
+    unsigned long long* ctr = ix->stats_on ? ix->counters : nullptr;
+    if (exact) {
+        CU(ix->qpad.ensure(nq * ix->dpad));
+        CU(ix->exact_scratch.ensure(exact_scratch_bytes((uint32_t)nq, (uint32_t)k, ix->dev.sm_count)));
+        // pad the queries to dpad floats per row (aligned float4 loads in the tile kernel)
+        CU(pad_queries(d_q, ix->qpad.p, (uint32_t)nq, ix->dims, ix->dpad, st));
+        ExactCorpus c{}; c.vecs = ix->vecs; c.sqn = ix->sqn; c.row_stride = ix->dpad; c.row_step = 1; c.first_slot = 0; c.n = ix->n_slots;
+        c.deleted = ix->deleted; c.slot_key = ix->slot_key; c.n_slots = ix->n_slots;
+        ExactQueries q{}; q.q = ix->qpad.p; q.stride = ix->dpad; q.nq = (uint32_t)nq; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = 0; q.self_step = 0;
+        ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
+        CU(launch_exact(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, sc, ix->dev, st));
+        return VS_OK;
+    }
+    const uint32_t efe = (uint32_t)std::max(ef ? ef : (size_t)ix->efS, k);
+    GraphView g = ix->view(ix->n_slots, ix->top_level);
+    cudaError_t e = launch_search(g, d_q, (uint32_t)nq, (uint32_t)k, efe, ix->dev, d_keys, d_dist, ctr, st);
+    if (e == cudaErrorInvalidConfiguration) return fail(VS_ERR_UNSUPPORTED, "search: ef / dims too large for one warp's shared memory");
+    CU(e);
+    return VS_OK;
+}
+
+}  // namespace
+
+
+// =============================================================== C ABI (include/vsann.h) ======
+extern "C" {
+
+vs_status vs_index_create(const vs_options* o, vs_index** out) {
+    if (!o || !out) return fail(VS_ERR_INVALID, "create: null argument");
+    *out = nullptr;
+    if (o->dims == 0) return fail(VS_ERR_DIMS, "create: dimensions == 0");
+    if (o->metric < 0 || o->metric > 2) return fail(VS_ERR_INVALID, "create: unknown metric");
+    const size_t M = o->connectivity ? o->connectivity : 16;
+    if (M < 2 || M > 16) return fail(VS_ERR_UNSUPPORTED, "create: connectivity must be in [2, 16] (level-0 row = 2M <= 32 links, one per lane)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(VS_ERR_CUDA, "create: no CUDA device (libvsann has no CPU fallback)"); }
+    if (o->device < 0 || o->device >= ndev) return fail(VS_ERR_INVALID, "create: bad device ordinal");
+    cudaDeviceProp prop{};
+    CU(cudaGetDeviceProperties(&prop, o->device));
+    if (prop.major < 10) return fail(VS_ERR_CUDA, "create: device is not Blackwell (sm_100a kernels only)");
+    CU(cudaSetDevice(o->device));
+    auto* ix = new vs_index();
+    ix->dims = (uint32_t)o->dims; ix->dpad = (ix->dims + 3u) & ~3u; ix->metric = o->metric;
+    ix->M = (uint32_t)M; ix->W0 = 2 * ix->M;
+    ix->efA = (uint32_t)(o->expansion_add ? o->expansion_add : 128);
+    ix->efS = (uint32_t)(o->expansion_search ? o->expansion_search : 64);
+    ix->max_batch = (uint32_t)(o->max_batch ? o->max_batch : 16384);
+    if (const char* e = getenv("VSANN_MAX_BATCH")) { const long v = atol(e); if (v > 0) ix->max_batch = (uint32_t)v; }
+    if (ix->max_batch < 32) ix->max_batch = 32;
+    ix->reserve_increment = o->capacity_hint ? o->capacity_hint : 1000000;   // usearch.rs:62
+    ix->dev.device = o->device; ix->dev.sm_count = prop.multiProcessorCount; ix->dev.smem_per_block = prop.sharedMemPerBlockOptin;
+    if (const char* e = getenv("VSANN_HASH_FACTOR")) { const long v = atol(e); if (v > 0) ix->dev.hash_factor = (uint32_t)v; }
+    vs_status s = VS_OK;
+    auto body = [&]() -> vs_status {
+        CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+        CU(cudaEventCreate(&ix->ev0)); CU(cudaEventCreate(&ix->ev1)); CU(cudaEventCreateWithFlags(&ix->user_ev, cudaEventDisableTiming));
+        CU(cudaMalloc(&ix->counters, 8 * sizeof(unsigned long long)));
+        CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
+        vs_status r = do_reserve(ix, ix->reserve_increment); if (r != VS_OK) return r;
+        r = setup_build_scratch(ix); if (r != VS_OK) return r;
+        CU(cudaStreamSynchronize(ix->stream));
+        return VS_OK;
+    };
+    s = body();
+    if (s != VS_OK) { std::string keep = g_err; vs_index_destroy(ix); g_err = keep; return s; }
+    *out = ix; return VS_OK;
+}
+
+void vs_index_destroy(vs_index* ix) {
+    if (!ix) return;
+    cudaSetDevice(ix->dev.device);
+    if (ix->stream) cudaStreamSynchronize(ix->stream);
+    cudaFree(ix->vecs); cudaFree(ix->sqn); cudaFree(ix->links0); cudaFree(ix->slot_key); cudaFree(ix->deleted);
+    for (int l = 1; l < MAX_LEVELS; ++l) cudaFree(ix->linksU[l]);
+    cudaFree(ix->lt.inbox_cnt); cudaFree(ix->lt.inbox_idx); cudaFree(ix->counters);
+    ix->build_scratch.release(); ix->exact_scratch.release(); ix->stage.release(); ix->tomb.release();
+    ix->qpad.release(); ix->qdense.release(); ix->out_d.release(); ix->out_k.release();
+    if (ix->ev0) cudaEventDestroy(ix->ev0); if (ix->ev1) cudaEventDestroy(ix->ev1); if (ix->user_ev) cudaEventDestroy(ix->user_ev);
+    if (ix->stream) cudaStreamDestroy(ix->stream);
+    cudaGetLastError();
+    delete ix;
+}
+
+vs_status vs_add_batch(vs_index* ix, size_t n, const uint64_t* keys, const float* vecs) {
+    if (!ix || (n && (!keys || !vecs))) return fail(VS_ERR_INVALID, "add: null argument");
+    std::lock_guard<std::mutex> g(ix->mu);
+    for (size_t i = 0; i < n; ++i) {
+        auto it = ix->pend_pos.find(keys[i]);
+        if (it != ix->pend_pos.end()) {   // replaced before it landed: overwrite in place
+            std::memcpy(ix->pend_vecs.data() + it->second * ix->dims, vecs + i * ix->dims, ix->dims * sizeof(float));
+            continue;
+        }
+        ix->pend_pos.emplace(keys[i], ix->pend_keys.size());
+        ix->pend_keys.push_back(keys[i]);
+        ix->pend_vecs.insert(ix->pend_vecs.end(), vecs + i * ix->dims, vecs + (i + 1) * ix->dims);
+    }
+    if (ix->pend_keys.size() >= ix->max_batch) return flush_locked(ix, nullptr, 0, nullptr);
+    return VS_OK;
+}
+vs_status vs_add(vs_index* ix, uint64_t key, const float* vec) { return vs_add_batch(ix, 1, &key, vec); }
+
+vs_status vs_add_batch_device(vs_index* ix, size_t n, const uint64_t* keys, const float* d_vecs) {
+    if (!ix || (n && (!keys || !d_vecs))) return fail(VS_ERR_INVALID, "add: null argument");
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    {   // keys must be distinct inside one device batch
+        std::unordered_map<uint64_t, int> seen; seen.reserve(n * 2);
+        for (size_t i = 0; i < n; ++i) if (!seen.emplace(keys[i], 1).second) return fail(VS_ERR_INVALID, "add_batch_device: duplicate key inside the batch");
+    }
+    CU(cudaStreamSynchronize(nullptr));   // rows were produced on the caller's (legacy default) stream or earlier
+    return flush_locked(ix, d_vecs, n, keys);
+}
+
+vs_status vs_remove(vs_index* ix, uint64_t key) {
+    if (!ix) return fail(VS_ERR_INVALID, "remove: null index");
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    auto it = ix->key_slot.find(key);
+    if (it == ix->key_slot.end()) return fail(VS_NOT_FOUND, "remove: key not found");
+    cudaSetDevice(ix->dev.device);
+    const uint32_t slot = it->second;
+    CU(ix->tomb.ensure(1));
+    CU(cudaMemcpyAsync(ix->tomb.p, &slot, 4, cudaMemcpyHostToDevice, ix->stream));
+    CU(launch_tombstone(ix->deleted, ix->tomb.p, 1, ix->stream));
+    CU(cudaStreamSynchronize(ix->stream));
+    ix->key_slot.erase(it); ix->live--;
+    return VS_OK;
+}
+
+vs_status vs_search_batch_device(vs_index* ix, size_t nq, const float* d_q, size_t k, size_t ef, int exact,
+                                 uint64_t* d_keys, float* d_dist, void* stream) {
+    if (!ix || (nq && (!d_q || !d_keys || !d_dist))) return fail(VS_ERR_INVALID, "search: null argument");
+    if (k == 0) return fail(VS_ERR_INVALID, "search: k == 0");
+    if (nq == 0) return VS_OK;
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    cudaSetDevice(ix->dev.device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+    s = wait_user(ix, st); if (s != VS_OK) return s;
+    s = search_device_locked(ix, nq, d_q, k, ef, exact, d_keys, d_dist, st); if (s != VS_OK) return s;
+    if (stream) { CU(cudaEventRecord(ix->user_ev, st)); ix->user_pending = true; }
+    else { CU(cudaStreamSynchronize(st)); }
+    return VS_OK;
+}
+
+vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, size_t ef, int exact,
+                          uint64_t* keys_out, float* dist_out, size_t* found) {
+    if (!ix || (nq && (!qs || !keys_out || !dist_out))) return fail(VS_ERR_INVALID, "search: null argument");
+    if (k == 0) return fail(VS_ERR_INVALID, "search: k == 0");
+    if (nq == 0) return VS_OK;
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    cudaSetDevice(ix->dev.device);
+    CU(ix->qdense.ensure(nq * ix->dims)); CU(ix->out_k.ensure(nq * k)); CU(ix->out_d.ensure(nq * k));
+    s = wait_user(ix, ix->stream); if (s != VS_OK) return s;
+    CU(cudaMemcpyAsync(ix->qdense.p, qs, nq * ix->dims * 4, cudaMemcpyHostToDevice, ix->stream));
+    s = search_device_locked(ix, nq, ix->qdense.p, k, ef, exact, ix->out_k.p, ix->out_d.p, ix->stream); if (s != VS_OK) return s;
+    CU(cudaMemcpyAsync(keys_out, ix->out_k.p, nq * k * 8, cudaMemcpyDeviceToHost, ix->stream));
+    CU(cudaMemcpyAsync(dist_out, ix->out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, ix->stream));
+    CU(cudaStreamSynchronize(ix->stream));
+    if (found) for (size_t i = 0; i < nq; ++i) { size_t f = 0; while (f < k && keys_out[i * k + f] != UINT64_MAX) ++f; found[i] = f; }
+    return VS_OK;
+}
+
+vs_status vs_search(vs_index* ix, const float* q, size_t k, uint64_t* keys_out, float* dist_out, size_t* found) {
+    return vs_search_batch(ix, 1, q, k, 0, 0, keys_out, dist_out, found);
+}
+
+size_t vs_count(vs_index* ix) {
+    if (!ix) return 0;
+    std::lock_guard<std::mutex> g(ix->mu);
+    flush_locked(ix, nullptr, 0, nullptr);
+    return ix->live;
+}
+size_t vs_capacity(vs_index* ix) { if (!ix) return 0; std::lock_guard<std::mutex> g(ix->mu); return ix->capacity; }
+vs_status vs_reserve(vs_index* ix, size_t cap) {
+    if (!ix) return fail(VS_ERR_INVALID, "reserve: null index");
+    std::lock_guard<std::mutex> g(ix->mu); return do_reserve(ix, cap);
+}
+vs_status vs_flush(vs_index* ix) {
+    if (!ix) return fail(VS_ERR_INVALID, "flush: null index");
+    std::lock_guard<std::mutex> g(ix->mu); return flush_locked(ix, nullptr, 0, nullptr);
+}
+
+vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
+    if (!ix || !o) return fail(VS_ERR_INVALID, "stats: null argument");
+    std::lock_guard<std::mutex> g(ix->mu);
+    std::memset(o, 0, sizeof(*o));
+    unsigned long long c[8];
+    cudaSetDevice(ix->dev.device);
+    CU(cudaStreamSynchronize(ix->stream));
+    CU(cudaMemcpy(c, ix->counters, sizeof(c), cudaMemcpyDeviceToHost));
+    o->count = ix->live; o->slots = ix->n_slots; o->capacity = ix->capacity; o->pending = ix->pend_keys.size();
+    o->search_queries = c[0]; o->search_dist_evals = c[1]; o->search_expansions = c[2];
+    o->build_vectors = ix->st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = ix->st_build_batches;
+    o->build_seconds = ix->st_build_seconds; o->device_bytes = ix->device_bytes + ix->build_scratch.n + ix->exact_scratch.n;
+    o->top_level = (uint32_t)ix->top_level;
+    return VS_OK;
+}
+vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; return VS_OK; }
+vs_status vs_reset_stats(vs_index* ix) {
+    if (!ix) return VS_ERR_INVALID;
+    std::lock_guard<std::mutex> g(ix->mu);
+    cudaSetDevice(ix->dev.device);
+    CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
+    CU(cudaStreamSynchronize(ix->stream));
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0;
+    return VS_OK;
+}
+
+vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k, const uint64_t* d_keys_in, const float* d_dist_in,
+                               uint64_t* d_keys_out, float* d_dist_out, void* stream) {
+    if (!d_keys_in || !d_dist_in || !d_keys_out || !d_dist_out) return fail(VS_ERR_INVALID, "merge: null argument");
+    CU(cudaSetDevice(device));
+    CU(launch_merge_topk((uint32_t)parts, (uint32_t)nq, (uint32_t)k, d_keys_in, d_dist_in, d_keys_out, d_dist_out, (cudaStream_t)stream));
+    if (!stream) CU(cudaStreamSynchronize(nullptr));
+    return VS_OK;
+}
+
+vs_status vs_export_level(vs_index* ix, uint32_t level, uint32_t* links_out, size_t* n_rows, size_t* row_width, uint64_t* slot_keys_out, size_t* slots) {
+    if (!ix || !n_rows || !row_width) return fail(VS_ERR_INVALID, "export: null argument");
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    if ((int)level >= ix->n_levels) return fail(VS_ERR_INVALID, "export: no such level");
+    const size_t st = ix->stride[level], nr = ix->n_slots ? (ix->n_slots - 1) / st + 1 : 0, w = level == 0 ? ix->W0 : ix->M;
+    *n_rows = nr; *row_width = w; if (slots) *slots = ix->n_slots;
+    cudaSetDevice(ix->dev.device);
+    if (links_out && nr) CU(cudaMemcpy(links_out, level == 0 ? ix->links0 : ix->linksU[level], nr * w * 4, cudaMemcpyDeviceToHost));
+    if (slot_keys_out && ix->n_slots) CU(cudaMemcpy(slot_keys_out, ix->slot_key, (size_t)ix->n_slots * 8, cudaMemcpyDeviceToHost));
+    return VS_OK;
+}
+
+const char* vs_last_error(void) { return g_err.c_str(); }
+const char* vs_version(void) { return "vsann-b200 0.1 sm_100a"; }
+
+}  // extern "C"

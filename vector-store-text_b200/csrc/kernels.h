@@ -1,0 +1,96 @@
+// kernels.h — host-visible launchers of the sm_100a kernels (internal to libvsann.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "common.cuh"
+
+namespace vsann {
+
+constexpr uint32_t INBOX_CAP = 32;     // reverse edges one row can receive per batch
+constexpr uint32_t KNN_BATCH = 32;     // intra-batch exact neighbours merged into the candidates
+
+struct DeviceInfo {
+    int device = 0;
+    int sm_count = 148;
+    size_t smem_per_block = 227 * 1024;
+    uint32_t hash_factor = 48;         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
+};
+
+struct SearchPlan { uint32_t efp, hsize, warps_per_block, blocks_per_sm; size_t smem; };
+
+// One insertion batch: slots [first_slot, first_slot + count). Level-l items are the slots
+// divisible by M^l; their per-level scratch index is slot / M^l - first_row[l].
+struct BuildBatch {
+    uint32_t first_slot, count;
+    int new_top;                               // top level once this batch has landed
+    uint32_t first_row[MAX_LEVELS];
+    uint32_t items[MAX_LEVELS];                // items on level l
+    uint32_t item_off[MAX_LEVELS + 1];         // prefix sums over levels (k_select work list)
+    uint32_t total_items;
+    uint32_t* cand_id[MAX_LEVELS];             // [items_l][efp] graph candidates, ascending
+    float* cand_d[MAX_LEVELS];
+    uint32_t* cand_n[MAX_LEVELS];              // [items_l]
+    uint32_t* knn_id[MAX_LEVELS];              // [items_l][kbp] intra-batch exact neighbours (may be null)
+    float* knn_d[MAX_LEVELS];
+};
+
+// Reverse-edge inbox machinery (K5). Rows of all levels share one index space:
+// global row = row_base[l] + slot / M^l.
+struct LinkTables {
+    uint32_t row_base[MAX_LEVELS];
+    uint32_t* inbox_cnt;      // [total_rows]  edges registered this batch (0 between batches)
+    uint32_t* inbox_idx;      // [total_rows]  -> touched index
+    uint32_t* n_edges;        // device scalars
+    uint32_t* n_touched;
+    uint32_t* edge_row;       // [edge_cap]
+    uint32_t* edge_src;       // [edge_cap]
+    uint32_t* touched_row;    // [edge_cap]
+    uint32_t* touched_slot;   // [edge_cap]
+    uint8_t* touched_level;   // [edge_cap]
+    uint32_t* inbox_fill;     // [edge_cap]
+    uint32_t* inbox;          // [edge_cap][INBOX_CAP]
+};
+
+// Exact (brute-force) search over a strided set of rows.
+struct ExactCorpus {
+    const float* vecs;        // first row
+    const float* sqn;         // squared norm of row i at sqn[i * row_step]
+    size_t row_stride;        // floats between consecutive corpus rows (dpad * row_step)
+    uint32_t row_step;        // slot step between consecutive rows
+    uint32_t first_slot;      // slot id of row 0
+    uint32_t n;               // rows
+    const uint32_t* deleted;  // tombstones by slot (may be null)
+    const uint64_t* slot_key; // tie-break keys by slot (null => tie-break by slot)
+    uint32_t n_slots;
+};
+struct ExactQueries {
+    const float* q;           // row i at q + i * stride
+    size_t stride;
+    uint32_t nq;
+    uint32_t dims, dpad;      // floats to read per row / padded length of corpus rows
+    uint32_t self_first;      // query i is slot self_first + i * self_step (excluded); self_step == 0 => no exclusion
+    uint32_t self_step;
+};
+struct ExactScratch {         // sized by exact_scratch_bytes
+    void* ptr; size_t bytes;
+};
+
+size_t exact_scratch_bytes(uint32_t nq, uint32_t k, int sm_count);
+// Outputs: ascending top-k per query. out_slots (u32, NONE padded) and/or out_keys (u64, UINT64_MAX padded).
+cudaError_t launch_exact(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
+                         uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
+                         const ExactScratch& scratch, const DeviceInfo& dev, cudaStream_t st);
+
+cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st);
+uint32_t build_efp(uint32_t ef);
+cudaError_t launch_build_search(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
+                                unsigned long long* counters, cudaStream_t st);
+cudaError_t launch_link(const GraphView& g, const BuildBatch& b, const LinkTables& t, uint32_t efp, uint32_t kbp, const DeviceInfo& dev,
+                        unsigned long long* counters, cudaStream_t st);
+cudaError_t launch_row_prepare(const float* d_src, float* vecs, float* sqn, uint32_t first, uint32_t n, uint32_t dims, uint32_t dpad, cudaStream_t st);
+cudaError_t launch_tombstone(uint32_t* deleted, const uint32_t* d_slots, uint32_t n, cudaStream_t st);
+cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* keys_in, const float* dist_in,
+                              uint64_t* keys_out, float* dist_out, cudaStream_t st);
+
+}  // namespace vsann
