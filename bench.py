@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (BASELINE.json: "index build vectors/s; ANN QPS at
+recall@10>=0.95"), on BASELINE configs[1]: SIFT-1M-shaped synthetic, 1M x 128-d f32 L2, M=16,
+10k queries, k=10, one B200 (N ranks => N shards of 1M vectors, weak scaling).
+
+A step = one pass of the 10k-query batch through the ANN search (K3) at the smallest ef whose
+recall@10 against exact ground truth is >= 0.95. `value` times that with everything resident in
+HBM; `e2e` times the same batch through the C ABI with host buffers (H2D + D2H inside). The
+index build (K4/K5) is timed once per run and reported in the `build` block.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n N] [--nq Q] [--dist clustered|gaussian]
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+D, K_NN, M, EF_ADD, EF_PARITY = 128, 10, 16, 128, 64
+EF_SWEEP = [16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024]
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--n", type=int, default=1_000_000, help="vectors per shard")
+    p.add_argument("--nq", type=int, default=10_000)
+    p.add_argument("--dist", default="clustered", choices=["clustered", "gaussian"])
+    p.add_argument("--cpu-sample", type=int, default=100_000)
+    p.add_argument("--no-cpu", action="store_true")
+    p.add_argument("--ef", type=int, default=0, help="skip the sweep and use this ef")
+    return p.parse_args()
+
+
+def gen(n, d, seed, dist, centres_seed=4242):
+    """NumPy PCG64 standard_normal float32, corpus seed 42, query seed 43; the clustered
+    variant draws 4096 Gaussian centres and adds 0.3-sigma noise (SIFT-like low intrinsic dimension)."""
+    rng = np.random.default_rng(seed)
+    if dist == "gaussian":
+        return rng.standard_normal((n, d), dtype=np.float32)
+    c = np.random.default_rng(centres_seed).standard_normal((4096, d), dtype=np.float32)
+    a = rng.integers(0, 4096, n)
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x *= np.float32(0.3)
+    x += c[a]
+    return x
+
+
+def recall(found, truth):
+    hit = 0
+    for f, t in zip(found, truth):
+        hit += len(np.intersect1d(f, t, assume_unique=False))
+    return hit / truth.size
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.proc = gpu, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def load_oracle(vst):
+    so = os.path.join(ROOT, "oracle", "liboracle_vsann.so")
+    if not os.path.exists(so):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
+    return vst.load_library(so, prefix="ovs_")
+
+
+def cpu_leg(vst, args, x, q, ef, steps, warmup):
+    """The CPU restatement (oracle, kind "port") on the host cores: build on a bounded sample, then
+    time the same ANN query path. SCYLLA_USEARCH_BACKGROUND_THREADS sets the thread count (README.md:14-15)."""
+    cores = int(os.environ.get("SCYLLA_USEARCH_BACKGROUND_THREADS", "0")) or (os.cpu_count() or 1)
+    n = min(args.cpu_sample, x.shape[0])
+    nq = min(2000, q.shape[0])
+    o = vst.VsIndex(D, metric=vst.Metric.L2SQ, connectivity=M, expansion_add=EF_ADD, expansion_search=EF_PARITY,
+                    capacity_hint=n, lib=load_oracle(vst))
+    o.set_threads(cores)
+    t0 = time.perf_counter()
+    o.add_batch(np.arange(n, dtype=np.uint64), x[:n])
+    tb = time.perf_counter() - t0
+    for _ in range(min(warmup, 1)):
+        o.search(q[:nq], K_NN, ef=ef)
+    ts = []
+    for _ in range(max(1, steps)):
+        t0 = time.perf_counter()
+        o.search(q[:nq], K_NN, ef=ef)
+        ts.append(time.perf_counter() - t0)
+        if sum(ts) > 20:
+            break
+    truth, _, _ = o.search(q[:200], K_NN, exact=True)
+    ak, _, _ = o.search(q[:200], K_NN, ef=ef)
+    st = o.stats()
+    out = {"value": nq / float(np.mean(ts)), "unit": "queries/s", "cores": cores, "kind": "port",
+           "sample": f"oracle HNSW (M={M}, ef_add={EF_ADD}) built on the first {n} vectors of the workload with {cores} threads; "
+                     f"{nq} queries, k={K_NN}, ef={ef}; reference usearch itself is unavailable on this box (no Rust toolchain, crate unpinned)",
+           "build_vectors_per_s": n / tb, "recall_at_10": recall(ak, truth), "steps": len(ts), "ms_per_step": 1e3 * float(np.mean(ts)),
+           "dist_evals_per_query": st["search_dist_evals"] / max(1, st["search_queries"])}
+    o.close()
+    return out
+
+
+def algorithmic_counts(vst, g, x, q, ef, sample=200):
+    """Work of the sequential algorithm (oracle beam, oracle/oracle_vsann.cpp ovs_graph_search) on the
+    GPU-built graph for a query sample: distance evaluations and expansions per query."""
+    olib = load_oracle(vst)
+    links0, _ = g.export_level(0)
+    n = x.shape[0]
+    uppers = []
+    lvl = 1
+    while M ** lvl < n:
+        uppers.append(g.export_level(lvl)[0])
+        lvl += 1
+    ev_tot, ex_tot = 0, 0
+    slots = np.zeros(K_NN, np.uint32); dist = np.zeros(K_NN, np.float32)
+    for i in range(min(sample, q.shape[0])):
+        qi = q[i]
+        cur, dcur = 0, float(((x[0] - qi) ** 2).sum())
+        ev, ex = 1, 0
+        for l in range(len(uppers), 0, -1):          # greedy descent on the upper levels
+            tab, stride = uppers[l - 1], M ** l
+            while True:
+                row = tab[cur // stride]; row = row[row != 0xFFFFFFFF]
+                ex += 1
+                if row.size == 0:
+                    break
+                dd = ((x[row] - qi) ** 2).sum(1); ev += row.size
+                j = int(dd.argmin())
+                if dd[j] < dcur:
+                    cur, dcur = int(row[j]), float(dd[j])
+                else:
+                    break
+        found, e1, e2 = C.c_size_t(), C.c_uint64(), C.c_uint64()
+        olib.ovs_graph_search(1, D, n, x.ctypes.data_as(C.c_void_p), links0.ctypes.data_as(C.c_void_p), links0.shape[1], None, cur,
+                              qi.ctypes.data_as(C.c_void_p), K_NN, ef, slots.ctypes.data_as(C.c_void_p), dist.ctypes.data_as(C.c_void_p),
+                              C.byref(found), C.byref(e1), C.byref(e2))
+        ev_tot += ev + e1.value; ex_tot += ex + e2.value
+    s = min(sample, q.shape[0])
+    return ev_tot / s, ex_tot / s
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores. The reference's
+    own code cannot run here (usearch crate absent/unpinned, no Rust), so this times the oracle port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import vector_store_text_b200 as vst
+    x = gen(min(args.n, args.cpu_sample), D, 42, args.dist)
+    q = gen(args.nq, D, 43, args.dist)
+    ef = args.ef or EF_PARITY
+    cb = cpu_leg(vst, args, x, q, ef, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": "ann_qps_at_recall95", "value": cb["value"], "unit": "queries/s", "n_gpus": args.gpus,
+            "steps": cb["steps"], "warmup": min(args.warmup, 1), "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "M": M, "ef_add": EF_ADD, "ef_search": ef, "k": K_NN},
+            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args):
+    return (f"configs[1] SIFT-1M-shaped synthetic: {args.n} x {D} f32 L2sq per shard ({args.dist}), M={M} ef_add={EF_ADD}, "
+            f"{args.nq} queries k={K_NN}")
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    import vector_store_text_b200 as vst
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = vst.load_library()          # the CUDA library is mandatory; raises if missing
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- data: shard r holds keys i * world + r (shard = key % world) -------------
+    n, nq = args.n, args.nq
+    x = gen(n, D, 42 + 1000 * rank, args.dist)
+    q = gen(nq, D, 43, args.dist)
+    keys = np.arange(n, dtype=np.uint64) * world + rank
+    xd = torch.from_numpy(x).to(dev)
+    qd = torch.from_numpy(q).to(dev)
+    torch.cuda.synchronize()
+
+    # ---- build (K4/K5), device-resident rows; timed once ------------------------------------------
+    g = vst.VsIndex(D, metric=vst.Metric.L2SQ, connectivity=M, expansion_add=EF_ADD, expansion_search=EF_PARITY,
+                    capacity_hint=n, device=local, lib=lib)
+    barrier()
+    t0 = time.perf_counter()
+    g.add_batch_device(keys, xd.data_ptr(), n)
+    torch.cuda.synchronize()
+    build_wall = max_over_ranks(time.perf_counter() - t0)
+    st = g.stats()
+    build_dev = max_over_ranks(st["build_seconds"])
+    assert g.count() == n
+
+    ok = torch.empty((nq, K_NN), dtype=torch.int64, device=dev)
+    od = torch.empty((nq, K_NN), dtype=torch.float32, device=dev)
+    gk = torch.empty((world, nq, K_NN), dtype=torch.int64, device=dev) if world > 1 else None
+    gd = torch.empty((world, nq, K_NN), dtype=torch.float32, device=dev) if world > 1 else None
+    mk = torch.empty((nq, K_NN), dtype=torch.int64, device=dev)
+    md = torch.empty((nq, K_NN), dtype=torch.float32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def search_step(ef, exact=False):
+        """One pass of the query batch: shard search, then (N > 1) all-gather + merge kernel (K6)."""
+        g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
+        if world == 1:
+            return ok
+        dist.all_gather_into_tensor(gk.view(-1), ok.view(-1))
+        dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
+        vst.merge_topk_device(local, world, nq, K_NN, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=lib)
+        return mk
+
+    truth = search_step(0, exact=True).cpu().numpy().view(np.uint64).copy()
+    torch.cuda.synchronize()
+
+    # ---- ef sweep: smallest ef with recall@10 >= 0.95, plus the M=16/ef=64 parity point ------------
+    sweep = {}
+    chosen = None
+    for ef in ([args.ef] if args.ef else EF_SWEEP):
+        try:
+            r = recall(search_step(ef).cpu().numpy().view(np.uint64), truth)
+        except vst.VsError as e:
+            sweep[ef] = f"unsupported: {e.message}"
+            break
+        sweep[ef] = round(r, 4)
+        if r >= 0.95 and chosen is None:
+            chosen = ef
+            if ef >= EF_PARITY:
+                break
+    if EF_PARITY not in sweep:
+        sweep[EF_PARITY] = round(recall(search_step(EF_PARITY).cpu().numpy().view(np.uint64), truth), 4)
+    reached = chosen is not None
+    if chosen is None:
+        chosen = max(e for e, r in sweep.items() if not isinstance(r, str))
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        tot = 0.0
+        for _ in range(steps):
+            flush_buf.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world > 1:
+                dist.barrier()
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            tot += e0.elapsed_time(e1)
+        barrier()
+        return max_over_ranks(tot / steps)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed(lambda: search_step(chosen), args.steps, args.warmup)
+    ms_parity = timed(lambda: search_step(EF_PARITY), max(2, args.steps // 2), 1)
+    # the search kernel alone (no collective) for the roofline
+    ms_kernel = timed(lambda: g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=chosen, stream=stream), args.steps, 1)
+
+    # ---- e2e: same batch through the C ABI with pinned HOST buffers (H2D + D2H inside) --------------
+    qh = torch.from_numpy(q).pin_memory()
+    kh = torch.empty((nq, K_NN), dtype=torch.int64).pin_memory()
+    dh = torch.empty((nq, K_NN), dtype=torch.float32).pin_memory()
+    fh = np.zeros(nq, dtype=np.uintp)
+    fn_host = getattr(lib, "vs_search_batch")
+
+    def e2e_step():
+        stt = fn_host(g._h, nq, C.c_void_p(qh.data_ptr()), K_NN, chosen, 0, C.c_void_p(kh.data_ptr()), C.c_void_p(dh.data_ptr()), fh.ctypes.data_as(C.c_void_p))
+        assert stt == 0
+        if world > 1:   # results come back to the host per shard; merge on device as the serving rank would
+            ok.copy_(kh, non_blocking=True); od.copy_(dh, non_blocking=True)
+            dist.all_gather_into_tensor(gk.view(-1), ok.view(-1)); dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
+            vst.merge_topk_device(local, world, nq, K_NN, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=lib)
+            kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
+            torch.cuda.synchronize()
+
+    for _ in range(max(1, args.warmup)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e_recall = recall(kh.numpy().view(np.uint64), truth)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+        ev, ex = algorithmic_counts(vst, g, x, q, chosen)
+        row_bytes = 2 * M * 4
+        alg_bytes = (ev * D * 4 + ex * row_bytes) * nq
+        achieved = alg_bytes / (ms_kernel * 1e-3) / 1e9
+        cb = None if args.no_cpu else cpu_leg(vst, args, x, q, chosen, 3, 1)
+        shard_q = world * nq
+        line = {
+            "metric": "ann_qps_at_recall95", "value": shard_q / (ms * 1e-3), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "corpus_total": n * world, "M": M, "ef_add": EF_ADD, "ef_search": chosen, "k": K_NN,
+                       "recall_at_10": sweep.get(chosen), "recall_target_reached": reached, "ef_sweep_recall": sweep,
+                       "l2": "corpus 512 MB + links 128 MB per shard exceed the 126 MB L2; a 256 MB buffer is rewritten between timed steps",
+                       "value_definition": "queries x shards / s: every rank answers every query on its own 1M-vector shard (N=1: plain QPS)",
+                       "parallelism": f"shard-by-key x{world}" + (" + nccl all_gather + merge kernel" if world > 1 else "")},
+            "global_qps": nq / (ms * 1e-3),
+            "parity_point": {"ef_search": EF_PARITY, "recall_at_10": sweep.get(EF_PARITY), "qps": shard_q / (ms_parity * 1e-3)},
+            "build": {"vectors_per_s": n * world / build_dev, "seconds_device": build_dev, "seconds_wall": build_wall,
+                      "batches": st["build_batches"], "unit": "vectors/s"},
+            "e2e": {"value": shard_q / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * D * 4, "d2h_bytes_per_step": nq * K_NN * 12,
+                    "ms_per_step": e2e_ms, "recall_at_10": e2e_recall},
+            "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "kernel": "k_search", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": None, "peak_source": peak_src, "kernel_ms": ms_kernel,
+                         "algorithmic": {"dist_evals_per_query": ev, "expansions_per_query": ex, "bytes_per_query": ev * D * 4 + ex * row_bytes,
+                                         "source": "oracle beam (ovs_graph_search) on the GPU-built graph, 200-query sample"}},
+            "cpu_baseline": cb, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    g.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -398,14 +398,17 @@ vs_status ovs_graph_search(int metric, size_t d, size_t n, const float* vecs, co
         DistId c = cand.top(); if (top.size() >= ef && c.d > top.top().d) break; cand.pop(); ++ex;
         for (size_t j = 0; j < width; ++j) {
             uint32_t s = links[(size_t)c.s * width + j]; if (s == NONE || s >= n) continue;
-            if (vis[s]) continue; vis[s] = 1; float dd = dist(s); ++ev;
-            if (top.size() < ef || dd < top.top().d || (dd == top.top().d && s < top.top().s)) { cand.push({dd, s}); top.push({dd, s}); if (top.size() > ef) top.pop(); }
+            if (vis[s]) continue;
+            vis[s] = 1; float dd = dist(s); ++ev;
+            if (top.size() < ef || dd < top.top().d) { cand.push({dd, s}); top.push({dd, s}); if (top.size() > ef) top.pop(); }
         }
     }
     std::vector<DistId> r(top.size()); for (size_t i = top.size(); i-- > 0;) { r[i] = top.top(); top.pop(); }
     size_t f = 0;
     for (auto& x : r) { if (deleted && deleted[x.s]) continue; if (f >= k) break; slots_out[f] = x.s; dist_out[f] = x.d; ++f; }
-    if (found) *found = f; if (evals_out) *evals_out = ev; if (exps_out) *exps_out = ex;
+    if (found) *found = f;
+    if (evals_out) *evals_out = ev;
+    if (exps_out) *exps_out = ex;
     return VS_OK;
 }
 

@@ -1,0 +1,240 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path through the C ABI against the CPU
+oracle on the same seeded inputs. Exact mode: bit-identical ids and distances. ANN mode: recall
+at least the oracle's at the same M/ef (minus sampling noise), and the traversal kernel agrees
+with the oracle's beam on the SAME exported graph."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import make_data, recall_at_k
+
+pytestmark = pytest.mark.gpu
+
+V1, V2, V3 = [1, 1, 1], [2, -2, 2], [3, 3, 3]
+
+
+def both(vst, oracle_lib, dims, metric, cap, **kw):
+    return (vst.VsIndex(dims, metric=metric, capacity_hint=cap, **kw),
+            vst.VsIndex(dims, metric=metric, capacity_hint=cap, lib=oracle_lib, **{k: v for k, v in kw.items() if k != "max_batch"}))
+
+
+@pytest.mark.parametrize("metric", [0, 1, 2])
+def test_kat_reference_unit_test(vst, metric):
+    """src/index/usearch.rs:323-425 through the host-side actor on the GPU library."""
+    a = vst.IndexActor("vector.ann", 3, metric=metric, capacity_hint=1000)
+    a.add_or_replace((1, "one"), V1); a.add_or_replace((2, "two"), V2); a.add_or_replace((3, "three"), V3)
+    assert a.count() == 3
+    pks, d = a.ann([2.2, -2.2, 2.2], 1)
+    assert pks == [(2, "two")] and len(d) == 1
+    a.add_or_replace((3, "three"), [2.1, -2.1, 2.1])
+    assert a.count() == 3
+    if metric != 0:
+        assert a.ann([2.2, -2.2, 2.2], 1)[0] == [(3, "three")]
+    a.remove((3, "three"))
+    assert a.count() == 2
+    assert a.ann([2.2, -2.2, 2.2], 1)[0] == [(2, "two")]
+    pks, d = a.ann([2.1, -2.0, 2.0], 1)          # tests/integration/usearch.rs:110-123
+    assert pks == [(2, "two")] and len(d) == 1
+    a.close()
+
+
+@pytest.mark.parametrize("metric", [0, 1, 2])
+@pytest.mark.parametrize("n,d,k", [(3000, 128, 10), (777, 33, 1), (5000, 96, 100), (130, 7, 10), (20000, 64, 10)])
+def test_exact_bit_identical(vst, oracle_lib, metric, n, d, k):
+    x = make_data(n, d, 11 + n); q = make_data(37 if n < 10000 else 300, d, 12 + n)
+    g, o = both(vst, oracle_lib, d, metric, 2 * n)
+    keys = np.arange(n, dtype=np.uint64) * 3 + 5
+    g.add_batch(keys, x); o.add_batch(keys, x)
+    gk, gd, gf = g.search(q, k, exact=True)
+    ok, od, of = o.search(q, k, exact=True)
+    assert np.array_equal(gf, of)
+    assert np.array_equal(gk, ok), "brute-force ids must be bit-identical to the oracle"
+    assert np.array_equal(gd.view(np.uint32), od.view(np.uint32)), "same fmaf chain => same bits"
+    g.close()
+
+
+def test_exact_with_duplicates_ties_removes_and_replaces(vst, oracle_lib):
+    d, n = 16, 600
+    x = make_data(n, d, 21)
+    x[100:200] = x[0:100]                       # exact duplicate rows => distance ties broken by key
+    q = np.concatenate([x[:20], make_data(20, d, 22)])
+    g, o = both(vst, oracle_lib, d, 1, 2000)
+    keys = np.random.default_rng(5).permutation(n).astype(np.uint64)   # slot order != key order
+    for ix in (g, o):
+        ix.add_batch(keys, x)
+        for kk in keys[5:50]:
+            assert ix.remove(int(kk))
+        ix.add_batch(keys[300:320], make_data(20, d, 23))             # replaces
+        assert not ix.remove(10 ** 9)
+    assert g.count() == o.count() == n - 45
+    gk, gd, gf = g.search(q, 25, exact=True)
+    ok, od, of = o.search(q, 25, exact=True)
+    assert np.array_equal(gk, ok) and np.array_equal(gd.view(np.uint32), od.view(np.uint32)) and np.array_equal(gf, of)
+    g.close()
+
+
+def test_small_and_empty(vst, oracle_lib):
+    g, o = both(vst, oracle_lib, 4, 1, 100)
+    for ix in (g, o):
+        for exact in (False, True):
+            k, dd, f = ix.search(np.zeros((2, 4), np.float32), 5, exact=exact)
+            assert f.tolist() == [0, 0] and np.all(k == np.uint64(2 ** 64 - 1)) and np.all(np.isinf(dd))
+        ix.add(7, [1, 0, 0, 0])
+        assert ix.count() == 1
+        for exact in (False, True):
+            k, dd = ix.search([0, 0, 0, 0], 5, exact=exact)
+            assert k.tolist() == [7] and dd.tolist() == [1.0]
+        ix.add(8, [0, 2, 0, 0]); ix.add(9, [0, 0, 3, 0])
+        k, dd = ix.search([0, 0, 0, 0], 5)
+        assert k.tolist() == [7, 8, 9] and dd.tolist() == [1.0, 4.0, 9.0]
+    with pytest.raises(vst.VsError):
+        g.add(1, [1, 2, 3])
+    g.close()
+
+
+def graph_invariants(links, n):
+    assert links.shape[0] >= n
+    for s in range(0, n, max(1, n // 500)):
+        row = links[s]; row = row[row != 0xFFFFFFFF]
+        assert np.all(row < n) and s not in row.tolist() and len(set(row.tolist())) == len(row)
+
+
+@pytest.mark.parametrize("metric,clustered", [(1, False), (1, True), (0, True), (2, True)])
+def test_ann_recall_not_below_oracle(vst, oracle_lib, metric, clustered):
+    n, d, nq = 20000, 64, 500
+    x = make_data(n, d, 31, clustered=clustered); q = make_data(nq, d, 32, clustered=clustered)
+    if metric == 2:
+        x /= np.linalg.norm(x, axis=1, keepdims=True); q /= np.linalg.norm(q, axis=1, keepdims=True)
+    g, o = both(vst, oracle_lib, d, metric, n, connectivity=16, expansion_add=128, expansion_search=64)
+    keys = np.arange(n, dtype=np.uint64)
+    o.set_threads(8)
+    g.add_batch(keys, x); o.add_batch(keys, x)
+    assert g.count() == n
+    truth, _, _ = g.search(q, 10, exact=True)
+    gk, gd, _ = g.search(q, 10)
+    okk, _, _ = o.search(q, 10)
+    rg, ro = recall_at_k(gk, truth), recall_at_k(okk, truth)
+    print(f"metric={metric} clustered={clustered} recall gpu={rg:.4f} oracle={ro:.4f}")
+    assert rg >= ro - 0.02, (rg, ro)
+    assert np.all(np.diff(gd, axis=1) >= 0)
+    links, skeys = g.export_level(0)
+    graph_invariants(links, n)
+    assert np.array_equal(skeys, keys)
+    g.close()
+
+
+def test_traversal_matches_oracle_on_same_graph(vst, oracle_lib):
+    """K3 vs the oracle's beam on the graph the GPU built (flat level 0, entry = the GPU's own
+    descent result is not exported, so use an index small enough to have a single level)."""
+    n, d, nq, ef, k = 15, 32, 64, 16, 5          # n <= M => top level 0, entry = slot 0
+    for n in (15, 16):
+        x = make_data(n, d, 41); q = make_data(nq, d, 42)
+        g = vst.VsIndex(d, metric=1, capacity_hint=64, connectivity=16)
+        g.add_batch(np.arange(n, dtype=np.uint64), x)
+        links, _ = g.export_level(0)
+        gk, gd, _ = g.search(q, k, ef=ef)
+        for i in range(nq):
+            slots = np.zeros(k, np.uint32); dist = np.zeros(k, np.float32); found = C.c_size_t()
+            st = oracle_lib.ovs_graph_search(1, d, n, x.ctypes.data_as(C.c_void_p), links.ctypes.data_as(C.c_void_p), links.shape[1], None, 0,
+                                             q[i].ctypes.data_as(C.c_void_p), k, ef, slots.ctypes.data_as(C.c_void_p),
+                                             dist.ctypes.data_as(C.c_void_p), C.byref(found), None, None)
+            assert st == 0 and found.value == k
+            assert gk[i].tolist() == slots.tolist()
+            np.testing.assert_allclose(gd[i], dist, rtol=1e-5)
+        g.close()
+
+
+def test_traversal_matches_oracle_large_graph(vst, oracle_lib):
+    """Same check on a multi-level index: the GPU beam from the oracle-visible entry (slot 0)
+    with a wide ef must return what the oracle's beam returns on the exported level-0 table."""
+    n, d, nq, ef, k = 4000, 32, 100, 256, 10
+    x = make_data(n, d, 43, clustered=True); q = make_data(nq, d, 44, clustered=True)
+    g = vst.VsIndex(d, metric=1, capacity_hint=n, connectivity=16)
+    g.add_batch(np.arange(n, dtype=np.uint64), x)
+    links, _ = g.export_level(0)
+    gk, gd, _ = g.search(q, k, ef=ef)
+    same = 0
+    for i in range(nq):
+        slots = np.zeros(k, np.uint32); dist = np.zeros(k, np.float32); found = C.c_size_t()
+        oracle_lib.ovs_graph_search(1, d, n, x.ctypes.data_as(C.c_void_p), links.ctypes.data_as(C.c_void_p), links.shape[1], None, 0,
+                                    q[i].ctypes.data_as(C.c_void_p), k, ef, slots.ctypes.data_as(C.c_void_p),
+                                    dist.ctypes.data_as(C.c_void_p), C.byref(found), None, None)
+        same += gk[i].tolist() == slots.tolist()
+    assert same >= 0.97 * nq, same     # different entry points (hierarchy vs slot 0) may differ on a few queries
+    g.close()
+
+
+def test_incremental_adds_removes_replace(vst, oracle_lib):
+    n, d = 6000, 48
+    x = make_data(n, d, 51, clustered=True); q = make_data(200, d, 52, clustered=True)
+    g = vst.VsIndex(d, metric=1, capacity_hint=1000, max_batch=512)        # forces capacity growth + many batches
+    keys = np.arange(n, dtype=np.uint64)
+    for i in range(0, n, 700):
+        g.add_batch(keys[i:i + 700], x[i:i + 700])
+    for i in range(100):
+        g.add(int(keys[i]), x[i])                                        # one-vector messages (replace)
+    assert g.count() == n and g.capacity() >= n
+    for kk in range(0, n, 3):
+        assert g.remove(kk)
+    live = n - len(range(0, n, 3))
+    assert g.count() == live
+    truth, _, tf = g.search(q, 10, exact=True)
+    ak, _, af = g.search(q, 10, ef=128)
+    assert np.all(tf == 10) and np.all(af == 10)
+    assert not np.any(ak % 3 == 0), "tombstoned keys must never be returned"
+    assert recall_at_k(ak, truth) > 0.9
+    st = g.stats()
+    assert st["count"] == live and st["slots"] == n + 100
+    g.close()
+
+
+def test_stats_counters(vst):
+    n, d = 3000, 32
+    x = make_data(n, d, 61)
+    g = vst.VsIndex(d, metric=1, capacity_hint=n)
+    g.set_stats(True)
+    g.add_batch(np.arange(n, dtype=np.uint64), x)
+    g.search(make_data(10, d, 62), 10)
+    s = g.stats()
+    assert s["search_queries"] == 10 and s["search_dist_evals"] > 10 * 64 and s["build_dist_evals"] > n * 64
+    assert s["build_vectors"] == n and s["build_seconds"] > 0
+    g.close()
+
+
+def test_merge_topk_device(vst):
+    import torch
+    parts, nq, k = 5, 77, 10
+    rng = np.random.default_rng(7)
+    dist = np.sort(rng.random((parts, nq, k), dtype=np.float32), axis=2)
+    keys = rng.permutation(parts * nq * k).astype(np.uint64).reshape(parts, nq, k)
+    dist[1, :, 3] = dist[2, :, 4]                                         # cross-part ties -> key order
+    dist = np.sort(dist, axis=2)
+    dk = torch.from_numpy(keys.view(np.int64)).cuda(); dd = torch.from_numpy(dist).cuda()
+    ok = torch.empty((nq, k), dtype=torch.int64, device="cuda"); od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    vst.merge_topk_device(0, parts, nq, k, dk.data_ptr(), dd.data_ptr(), ok.data_ptr(), od.data_ptr())
+    torch.cuda.synchronize()
+    for i in range(nq):
+        allp = sorted(zip(dist[:, i, :].ravel().tolist(), keys[:, i, :].ravel().tolist()))[:k]
+        assert od[i].cpu().tolist() == [p[0] for p in allp]
+        assert ok[i].cpu().numpy().view(np.uint64).tolist() == [p[1] for p in allp]
+
+
+def test_device_resident_search_and_add(vst):
+    import torch
+    n, d, nq, k = 5000, 64, 256, 10
+    x = torch.from_numpy(make_data(n, d, 71, clustered=True)).cuda(); q = torch.from_numpy(make_data(nq, d, 72, clustered=True)).cuda()
+    torch.cuda.synchronize()
+    g = vst.VsIndex(d, metric=1, capacity_hint=n)
+    g.add_batch_device(np.arange(n, dtype=np.uint64), x.data_ptr(), n)
+    assert g.count() == n
+    ok = torch.empty((nq, k), dtype=torch.int64, device="cuda"); od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    g.search_device(nq, q.data_ptr(), k, ok.data_ptr(), od.data_ptr(), exact=True)
+    hk, hd, _ = g.search(q.cpu().numpy(), k, exact=True)
+    assert np.array_equal(ok.cpu().numpy().view(np.uint64), hk) and np.array_equal(od.cpu().numpy(), hd)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        g.search_device(nq, q.data_ptr(), k, ok.data_ptr(), od.data_ptr(), ef=64, stream=st.cuda_stream)
+    st.synchronize()
+    assert recall_at_k(ok.cpu().numpy().view(np.uint64), hk) > 0.9
+    g.close()
