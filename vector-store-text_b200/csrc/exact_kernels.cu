@@ -45,6 +45,12 @@ size_t exact_scratch_bytes(uint32_t nq, uint32_t k, int sm_count) {
     return b;
 }
 
+// Upper bound of exact_scratch_bytes over every nq <= max_nq: nq * chunks(nq) <= 256 * sm + nq.
+size_t exact_scratch_bytes_upto(uint32_t max_nq, uint32_t k, int sm_count) {
+    const size_t kp = (k + 31u) & ~31u, rows = (size_t)256 * sm_count + max_nq;
+    return (((size_t)max_nq * 4 + 255) & ~(size_t)255) + ((rows + 255) & ~(size_t)255) + rows * 2 * kp * 8 + 512;
+}
+
 __global__ void k_query_norms(ExactQueries q, float* qn) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= q.nq) return;

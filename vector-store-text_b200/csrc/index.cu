@@ -65,7 +65,7 @@ template <class T> struct DBuf {
 struct vs_index {
     // options
     uint32_t dims = 0, dpad = 0; int metric = 0; uint32_t M = 16, W0 = 32, efA = 128, efS = 64;
-    uint32_t max_batch = 16384; size_t reserve_increment = 1000000;
+    uint32_t max_batch = 16384, batch_div = 16; size_t reserve_increment = 1000000;
     DeviceInfo dev; cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, user_ev = nullptr; bool user_pending = false;
     std::mutex mu;
     // tables
@@ -180,7 +180,7 @@ vs_status setup_build_scratch(vs_index* ix) {
     ix->lt.edge_row = (uint32_t*)(p + o_er); ix->lt.edge_src = (uint32_t*)(p + o_es);
     ix->lt.touched_row = (uint32_t*)(p + o_tr); ix->lt.touched_slot = (uint32_t*)(p + o_ts); ix->lt.touched_level = (uint8_t*)(p + o_tl);
     ix->lt.inbox_fill = (uint32_t*)(p + o_if); ix->lt.inbox = (uint32_t*)(p + o_in);
-    CU(ix->exact_scratch.ensure(exact_scratch_bytes(B, KNN_BATCH, ix->dev.sm_count)));
+    CU(ix->exact_scratch.ensure(exact_scratch_bytes_upto(B, KNN_BATCH, ix->dev.sm_count)));
     return VS_OK;
 }
 
@@ -259,7 +259,9 @@ vs_status flush_locked(vs_index* ix, const float* d_rows /* device rows or null 
     size_t done = 0;
     while (done < n) {
         const uint32_t cur = base + (uint32_t)done;
-        uint32_t bsz = cur == 0 ? 1024u : cur;                 // bootstrap block, then at most doubling
+        // bootstrap block (all-pairs), then batches of at most 1/batch_div of the landed graph so
+        // that almost every candidate a new node needs is already linked (recall vs batch size: DESIGN.md)
+        uint32_t bsz = cur == 0 ? 1024u : std::max(256u, cur / ix->batch_div);
         bsz = (uint32_t)std::min<size_t>({(size_t)bsz, (size_t)ix->max_batch, n - done});
         vs_status s = insert_batch(ix, cur, bsz); if (s != VS_OK) return s;
         done += bsz;
@@ -330,6 +332,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     ix->max_batch = (uint32_t)(o->max_batch ? o->max_batch : 16384);
     if (const char* e = getenv("VSANN_MAX_BATCH")) { const long v = atol(e); if (v > 0) ix->max_batch = (uint32_t)v; }
     if (ix->max_batch < 32) ix->max_batch = 32;
+    if (const char* e = getenv("VSANN_BATCH_DIV")) { const long v = atol(e); if (v > 0) ix->batch_div = (uint32_t)v; }
     ix->reserve_increment = o->capacity_hint ? o->capacity_hint : 1000000;   // usearch.rs:62
     ix->dev.device = o->device; ix->dev.sm_count = prop.multiProcessorCount; ix->dev.smem_per_block = prop.sharedMemPerBlockOptin;
     if (const char* e = getenv("VSANN_HASH_FACTOR")) { const long v = atol(e); if (v > 0) ix->dev.hash_factor = (uint32_t)v; }

@@ -76,6 +76,7 @@ struct ExactScratch {         // sized by exact_scratch_bytes
 };
 
 size_t exact_scratch_bytes(uint32_t nq, uint32_t k, int sm_count);
+size_t exact_scratch_bytes_upto(uint32_t max_nq, uint32_t k, int sm_count);
 // Outputs: ascending top-k per query. out_slots (u32, NONE padded) and/or out_keys (u64, UINT64_MAX padded).
 cudaError_t launch_exact(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
                          uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
