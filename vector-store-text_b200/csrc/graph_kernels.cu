@@ -25,7 +25,7 @@ __device__ __forceinline__ void warp_load_query(float4* q4, const float* q, uint
 }
 
 // ---------------------------------------------------------------- K3: ANN search ------------
-__global__ void __launch_bounds__(128) k_search(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+__global__ void __launch_bounds__(128, 8) k_search(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                 uint32_t ef, uint32_t efp, uint32_t hsize,
                                                 uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                 unsigned long long* counters) {
@@ -300,7 +300,7 @@ static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t s
     SearchPlan p;
     p.efp = (ef + 31u) & ~31u;
     uint32_t hs = next_pow2(ef * hash_factor);
-    if (hs < 1024) hs = 1024;
+    if (hs < 512) hs = 512;
     if (hs > 16384) hs = 16384;
     size_t per_warp = warp_smem_bytes(dpad, p.efp, hs);
     while (per_warp > smem_limit && hs > 256) { hs >>= 1; per_warp = warp_smem_bytes(dpad, p.efp, hs); }
@@ -323,9 +323,8 @@ cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t n
     if (p.smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
     if (e != cudaSuccess) return e;
-    uint32_t blocks = (nq + p.warps_per_block - 1) / p.warps_per_block;
-    const uint32_t maxb = dev.sm_count * p.blocks_per_sm;
-    if (blocks > maxb) blocks = maxb;
+    // one warp per query, one block per 4 queries: the hardware block scheduler balances the tail
+    const uint32_t blocks = (nq + p.warps_per_block - 1) / p.warps_per_block;
     k_search<<<blocks, p.warps_per_block * 32, p.smem, st>>>(g, d_queries, nq, k, ef, p.efp, p.hsize, d_keys, d_dist, counters);
     return cudaGetLastError();
 }
