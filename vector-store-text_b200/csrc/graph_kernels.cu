@@ -4,7 +4,7 @@
 // Reference behaviour restated: usearch::Index::search (src/index/usearch.rs:276) and
 // usearch::Index::add (src/index/usearch.rs:221); algorithm per SURVEY.md Appendix B, CPU
 // restatement in oracle/oracle_vsann.cpp (hnsw_search / hnsw_insert / select_heuristic).
-#include "beam.cuh"
+#include "rbeam.cuh"
 #include "kernels.h"
 
 namespace vsann {
@@ -54,6 +54,50 @@ __global__ void __launch_bounds__(128, 8) k_search(GraphView g, const float* __r
                 const unsigned m = __ballot_sync(0xffffffffu, live);
                 const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
                 if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = d; }
+                nout += __popc(m);
+            }
+            if (nout > k) nout = k;
+        }
+        for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
+        ++done;
+        __syncwarp();
+    }
+    if (counters && lane == 0) {
+        atomicAdd(&counters[0], (unsigned long long)done);
+        atomicAdd(&counters[1], (unsigned long long)evals);
+        atomicAdd(&counters[2], (unsigned long long)exps);
+    }
+}
+
+// Register-list variant (ef <= 32 * NL): the hot configuration of K3.
+template <int NL>
+__global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+                                                     uint32_t ef, uint32_t hsize,
+                                                     uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
+                                                     unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, 0, hsize);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 0, 0, hsize);
+    uint32_t evals = 0, exps = 0, done = 0;
+    for (uint32_t q = blockIdx.x * wpb + warp; q < nq; q += gridDim.x * wpb) {
+        warp_load_query(S.q4, queries + (size_t)q * g.dims, g.dims, g.dpad);
+        uint64_t* ko = keys_out + (size_t)q * k; float* dd = dist_out + (size_t)q * k;
+        uint32_t nout = 0;
+        if (g.n_slots > 0) {
+            const float qn = g.metric == COS ? warp_sqnorm(S.q4, g.chunks) : 0.f;
+            uint32_t cur = 0; float dcur = warp_entry_dist(g, S, qn, 0u, evals);
+            for (int l = g.top_level; l >= 1; --l) greedy_level(g, l, S, qn, cur, dcur, evals, exps);
+            RList<NL> L;
+            rbeam_seed(S, L, (int)ef, cur, dcur);
+            rbeam_level(g, 0, S, L, qn, evals, exps);
+#pragma unroll
+            for (int j = 0; j < NL; ++j) {
+                const uint32_t id = L.id[j] & ~EXPANDED;
+                const bool live = L.id[j] != NONE && !is_deleted(g, id);
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
+                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
                 nout += __popc(m);
             }
             if (nout > k) nout = k;
@@ -316,14 +360,34 @@ static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t s
     return p;
 }
 
+template <int NL>
+static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                                   uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    uint32_t hs = next_pow2(ef * dev.hash_factor);
+    if (hs < 512) hs = 512;
+    if (hs > 16384) hs = 16384;
+    const uint32_t wpb = 4;
+    const size_t smem = warp_smem_bytes(g.dpad, 0, hs) * wpb;
+    if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_search_r<NL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_search_r<NL><<<(nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, d_queries, nq, k, ef, hs, d_keys, d_dist, counters);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                           uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
     if (nq == 0) return cudaSuccess;
+    if (!dev.force_smem_list) {
+        if (ef <= 32) return launch_search_r<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (ef <= 64) return launch_search_r<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (ef <= 128) return launch_search_r<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (ef <= 256) return launch_search_r<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+    }
     const SearchPlan p = plan_search(g.dpad, ef, dev.sm_count, dev.smem_per_block, dev.hash_factor);
     if (p.smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
     if (e != cudaSuccess) return e;
-    // one warp per query, one block per 4 queries: the hardware block scheduler balances the tail
     const uint32_t blocks = (nq + p.warps_per_block - 1) / p.warps_per_block;
     k_search<<<blocks, p.warps_per_block * 32, p.smem, st>>>(g, d_queries, nq, k, ef, p.efp, p.hsize, d_keys, d_dist, counters);
     return cudaGetLastError();
