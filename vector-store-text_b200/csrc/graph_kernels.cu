@@ -157,6 +157,48 @@ __global__ void __launch_bounds__(128) k_build_search(GraphView g, BuildBatch b,
     if (counters && lane == 0) { atomicAdd(&counters[3], (unsigned long long)evals); atomicAdd(&counters[4], (unsigned long long)exps); }
 }
 
+// Register-list variant of K4a (ef_add <= 32 * NL).
+template <int NL>
+__global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize,
+                                                           unsigned long long* counters) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = warp_smem_bytes(g.dpad, 0, hsize);
+    WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 0, 0, hsize);
+    uint32_t evals = 0, exps = 0;
+    for (uint32_t it = blockIdx.x * wpb + warp; it < b.count; it += gridDim.x * wpb) {
+        const uint32_t slot = b.first_slot + it;
+        int lvl = 0;
+        while (lvl + 1 <= b.new_top && slot % g.stride[lvl + 1] == 0) ++lvl;
+        for (int l = 0; l <= lvl; ++l) {
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            if (lane == 0) b.cand_n[l][idx] = 0;
+        }
+        if (g.n_slots == 0) continue;
+        const float qn = warp_load_row(g, S.q4, slot);
+        uint32_t cur = 0; float dcur = warp_entry_dist(g, S, qn, 0u, evals);
+        for (int l = g.top_level; l > lvl; --l) greedy_level(g, l, S, qn, cur, dcur, evals, exps);
+        RList<NL> L;
+        rbeam_seed(S, L, (int)ef, cur, dcur);
+        for (int l = min(lvl, g.top_level); l >= 0; --l) {
+            rbeam_level(g, l, S, L, qn, evals, exps);
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
+            uint32_t n = 0;
+#pragma unroll
+            for (int j = 0; j < NL; ++j) {
+                const int i = j * 32 + lane;
+                if (i < (int)efp) { ci[i] = L.id[j] == NONE ? NONE : (L.id[j] & ~EXPANDED); cd[i] = L.d[j]; }
+                n += __popc(__ballot_sync(0xffffffffu, L.id[j] != NONE));
+            }
+            for (int i = NL * 32 + lane; i < (int)efp; i += 32) { ci[i] = NONE; cd[i] = INFINITY; }
+            if (lane == 0) b.cand_n[l][idx] = n;
+            if (l > 0) rbeam_reseed(S, L);
+        }
+    }
+    if (counters && lane == 0) { atomicAdd(&counters[3], (unsigned long long)evals); atomicAdd(&counters[4], (unsigned long long)exps); }
+}
+
 // ------------------------------------------------- heuristic selection (shared by K4b / K5) ---
 // Candidates arrive ascending by distance to the base through next(); a candidate is kept iff
 // it is at least as close to the base as to every neighbour kept so far. The kept ids live one
@@ -344,7 +386,7 @@ static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t s
     SearchPlan p;
     p.efp = (ef + 31u) & ~31u;
     uint32_t hs = next_pow2(ef * hash_factor);
-    if (hs < 512) hs = 512;
+    if (hs < 1024) hs = 1024;
     if (hs > 16384) hs = 16384;
     size_t per_warp = warp_smem_bytes(dpad, p.efp, hs);
     while (per_warp > smem_limit && hs > 256) { hs >>= 1; per_warp = warp_smem_bytes(dpad, p.efp, hs); }
@@ -364,7 +406,7 @@ template <int NL>
 static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
     uint32_t hs = next_pow2(ef * dev.hash_factor);
-    if (hs < 512) hs = 512;
+    if (hs < 1024) hs = 1024;
     if (hs > 16384) hs = 16384;
     const uint32_t wpb = 4;
     const size_t smem = warp_smem_bytes(g.dpad, 0, hs) * wpb;
@@ -395,16 +437,35 @@ cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t n
 
 uint32_t build_efp(uint32_t ef) { return (ef + 31u) & ~31u; }
 
+template <int NL>
+static cudaError_t launch_build_search_r(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
+                                         unsigned long long* counters, cudaStream_t st) {
+    uint32_t hs = next_pow2(ef * dev.hash_factor);
+    if (hs < 1024) hs = 1024;
+    if (hs > 16384) hs = 16384;
+    const uint32_t wpb = 4;
+    const size_t smem = warp_smem_bytes(g.dpad, 0, hs) * wpb;
+    if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_build_search_r<NL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_build_search_r<NL><<<(b.count + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, b, ef, build_efp(ef), hs, counters);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_build_search(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
                                 unsigned long long* counters, cudaStream_t st) {
+    if (b.count == 0) return cudaSuccess;
+    if (!dev.force_smem_list) {
+        if (ef <= 32) return launch_build_search_r<1>(g, b, ef, dev, counters, st);
+        if (ef <= 64) return launch_build_search_r<2>(g, b, ef, dev, counters, st);
+        if (ef <= 128) return launch_build_search_r<4>(g, b, ef, dev, counters, st);
+        if (ef <= 256) return launch_build_search_r<8>(g, b, ef, dev, counters, st);
+    }
     const SearchPlan p = plan_search(g.dpad, ef, dev.sm_count, dev.smem_per_block, dev.hash_factor);
     if (p.smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_build_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
     if (e != cudaSuccess) return e;
-    uint32_t blocks = (b.count + p.warps_per_block - 1) / p.warps_per_block;
-    const uint32_t maxb = dev.sm_count * p.blocks_per_sm;
-    if (blocks > maxb) blocks = maxb;
-    if (blocks == 0) return cudaSuccess;
+    const uint32_t blocks = (b.count + p.warps_per_block - 1) / p.warps_per_block;
     k_build_search<<<blocks, p.warps_per_block * 32, p.smem, st>>>(g, b, ef, p.efp, p.hsize, counters);
     return cudaGetLastError();
 }

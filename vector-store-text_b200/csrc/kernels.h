@@ -13,7 +13,7 @@ struct DeviceInfo {
     int device = 0;
     int sm_count = 148;
     size_t smem_per_block = 227 * 1024;
-    uint32_t hash_factor = 24;
+    uint32_t hash_factor = 16;
     bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
 };
 
