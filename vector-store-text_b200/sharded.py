@@ -1,0 +1,97 @@
+"""Sharded index: one process per GPU, corpus sharded by key.
+
+  shard(key) = key mod world_size           — a replaced key stays on its shard
+  add / remove                              — routed to the owning rank, no collective
+  ann                                       — every rank searches its shard with the full ef, one
+                                              all_gather of (dist f32, key u64)[B x k] per rank, then a
+                                              G-way merge per query (K6, csrc k_merge_topk)
+  count                                     — all_reduce(sum) of the shard counts
+
+The collective is `torch.distributed` (NCCL over NVLink on the GPU box; gloo in the CPU tests, where
+the local shard is the oracle backend and the merge below runs on host tensors — test plumbing only).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ._ffi import VsIndex, merge_topk_device
+
+
+def shard_of(keys, world):
+    return np.asarray(keys, dtype=np.uint64) % np.uint64(world)
+
+
+def merge_topk_host(keys, dists, k):
+    """Reference merge on host tensors: keys/dists [G, nq, k] ascending per part -> [nq, k] by (dist, key).
+    Used by the gloo tests and as the checker of the CUDA merge kernel."""
+    g, nq, _ = dists.shape
+    d = dists.permute(1, 0, 2).reshape(nq, -1).numpy()
+    kk = keys.permute(1, 0, 2).reshape(nq, -1).numpy().view(np.uint64)
+    order = np.lexsort((kk, d), axis=1)[:, :k]
+    return torch.from_numpy(np.take_along_axis(kk, order, 1).view(np.int64).copy()), torch.from_numpy(np.take_along_axis(d, order, 1).copy())
+
+
+class ShardedIndex:
+    def __init__(self, dims, rank=None, world=None, device=None, lib=None, **opts):
+        self.rank = dist.get_rank() if rank is None else rank
+        self.world = dist.get_world_size() if world is None else world
+        self.cuda = device is not None
+        self.device = device
+        self.local = VsIndex(dims, device=(device.index if self.cuda else 0), lib=lib, **opts)
+        self.dims = dims
+        self._lib = lib
+
+    # -- mutation: each rank is handed the full batch and keeps its own keys -----------------------
+    def add_batch(self, keys, vecs):
+        keys = np.asarray(keys, dtype=np.uint64)
+        mine = shard_of(keys, self.world) == np.uint64(self.rank)
+        if mine.any():
+            self.local.add_batch(keys[mine], np.asarray(vecs, dtype=np.float32)[mine])
+
+    def remove(self, key):
+        if int(key) % self.world == self.rank:
+            return self.local.remove(key)
+        return False
+
+    def count(self):
+        t = torch.tensor([self.local.count()], dtype=torch.int64, device=self.device if self.cuda else "cpu")
+        dist.all_reduce(t)
+        return int(t.item())
+
+    # -- search ---------------------------------------------------------------------------------------
+    def ann(self, queries, k, ef=0, exact=False):
+        """queries: [nq, dims] float32 (identical on every rank). Returns (keys u64 [nq,k], dists [nq,k])."""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        nq = q.shape[0]
+        if self.cuda:
+            qd = torch.from_numpy(q).to(self.device)
+            ok = torch.empty((nq, k), dtype=torch.int64, device=self.device)
+            od = torch.empty((nq, k), dtype=torch.float32, device=self.device)
+            mk, md = self.ann_device(qd, ok, od, k, ef, exact)
+            return mk.cpu().numpy().view(np.uint64), md.cpu().numpy()
+        lk, ld, _ = self.local.search(q, k, ef=ef, exact=exact)
+        ok = torch.from_numpy(lk.view(np.int64).copy()); od = torch.from_numpy(ld.copy())
+        gk = torch.empty((self.world, nq, k), dtype=torch.int64); gd = torch.empty((self.world, nq, k), dtype=torch.float32)
+        dist.all_gather_into_tensor(gk.view(-1), ok.view(-1))
+        dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
+        mk, md = merge_topk_host(gk, gd, k)
+        return mk.numpy().view(np.uint64), md.numpy()
+
+    def ann_device(self, qd, ok, od, k, ef=0, exact=False, gk=None, gd=None, mk=None, md=None):
+        """Device-resident path on the current torch stream: shard search -> all_gather -> merge kernel."""
+        nq = qd.shape[0]
+        stream = torch.cuda.current_stream().cuda_stream
+        self.local.search_device(nq, qd.data_ptr(), k, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
+        if self.world == 1:
+            return ok, od
+        gk = torch.empty((self.world, nq, k), dtype=torch.int64, device=self.device) if gk is None else gk
+        gd = torch.empty((self.world, nq, k), dtype=torch.float32, device=self.device) if gd is None else gd
+        mk = torch.empty_like(ok) if mk is None else mk
+        md = torch.empty_like(od) if md is None else md
+        dist.all_gather_into_tensor(gk.view(-1), ok.view(-1))
+        dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
+        merge_topk_device(self.device.index, self.world, nq, k, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=self._lib)
+        return mk, md
+
+    def close(self):
+        self.local.close()
