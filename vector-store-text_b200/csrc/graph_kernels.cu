@@ -4,7 +4,7 @@
 // Reference behaviour restated: usearch::Index::search (src/index/usearch.rs:276) and
 // usearch::Index::add (src/index/usearch.rs:221); algorithm per SURVEY.md Appendix B, CPU
 // restatement in oracle/oracle_vsann.cpp (hnsw_search / hnsw_insert / select_heuristic).
-#include "rbeam.cuh"
+#include "tbeam.cuh"
 #include "kernels.h"
 
 namespace vsann {
@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(128, 8) k_search(GraphView g, const float* __r
                                                 uint32_t ef, uint32_t efp, uint32_t hsize,
                                                 uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                 unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, efp, hsize);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, ef, efp, hsize);
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
                                                      uint32_t ef, uint32_t hsize,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                      unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, 0, hsize);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 0, 0, hsize);
@@ -113,13 +113,60 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
     }
 }
 
+// Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
+// float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
+template <int NL, int CPL>
+__global__ void __launch_bounds__(128, 4) k_search_t(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+                                                     uint32_t ef, uint32_t hsize, uint32_t stage_rows,
+                                                     uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
+                                                     unsigned long long* counters) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
+    WarpSmem S; WarpStage T;
+    carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
+    uint32_t evals = 0, exps = 0, done = 0;
+    for (uint32_t q = blockIdx.x * wpb + warp; q < nq; q += gridDim.x * wpb) {
+        warp_load_query(S.q4, queries + (size_t)q * g.dims, g.dims, g.dpad);
+        QRegs<CPL> Q; Q.load(S.q4);
+        uint64_t* ko = keys_out + (size_t)q * k; float* dd = dist_out + (size_t)q * k;
+        uint32_t nout = 0;
+        if (g.n_slots > 0) {
+            const float qn = g.metric == COS ? warp_sqnorm(S.q4, g.chunks) : 0.f;
+            uint32_t cur = 0; float dcur = stage_entry_dist<CPL>(g, S, T, Q, qn, 0u, evals);
+            for (int l = g.top_level; l >= 1; --l) tgreedy_level<CPL>(g, l, S, T, Q, qn, cur, dcur, evals, exps);
+            RList<NL> L;
+            rbeam_seed(S, L, (int)ef, cur, dcur);
+            tbeam_level<NL, CPL>(g, 0, S, T, Q, L, qn, evals, exps);
+#pragma unroll
+            for (int j = 0; j < NL; ++j) {
+                const uint32_t id = L.id[j] & ~EXPANDED;
+                const bool live = L.id[j] != NONE && !is_deleted(g, id);
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
+                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
+                nout += __popc(m);
+            }
+            if (nout > k) nout = k;
+        }
+        for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
+        ++done;
+        __syncwarp();
+    }
+    if (counters && lane == 0) {
+        atomicAdd(&counters[0], (unsigned long long)done);
+        atomicAdd(&counters[1], (unsigned long long)evals);
+        atomicAdd(&counters[2], (unsigned long long)exps);
+    }
+}
+
 // ------------------------------------------------- K4a: insertion search on the frozen graph --
 // One warp per batch item: greedy descent from the top, then an ef_add beam on every level the
 // item lives on; each level's sorted candidate list goes to scratch (cand_id / cand_d).
 // Level-l lists of the items with slot % M^l == 0 are stored at item index (slot/M^l - first_row[l]).
 __global__ void __launch_bounds__(128) k_build_search(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize,
                                                       unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, efp, hsize);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, ef, efp, hsize);
@@ -161,7 +208,7 @@ __global__ void __launch_bounds__(128) k_build_search(GraphView g, BuildBatch b,
 template <int NL>
 __global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize,
                                                            unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, 0, hsize);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 0, 0, hsize);
@@ -182,6 +229,50 @@ __global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBat
         rbeam_seed(S, L, (int)ef, cur, dcur);
         for (int l = min(lvl, g.top_level); l >= 0; --l) {
             rbeam_level(g, l, S, L, qn, evals, exps);
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
+            uint32_t n = 0;
+#pragma unroll
+            for (int j = 0; j < NL; ++j) {
+                const int i = j * 32 + lane;
+                if (i < (int)efp) { ci[i] = L.id[j] == NONE ? NONE : (L.id[j] & ~EXPANDED); cd[i] = L.d[j]; }
+                n += __popc(__ballot_sync(0xffffffffu, L.id[j] != NONE));
+            }
+            for (int i = NL * 32 + lane; i < (int)efp; i += 32) { ci[i] = NONE; cd[i] = INFINITY; }
+            if (lane == 0) b.cand_n[l][idx] = n;
+            if (l > 0) rbeam_reseed(S, L);
+        }
+    }
+    if (counters && lane == 0) { atomicAdd(&counters[3], (unsigned long long)evals); atomicAdd(&counters[4], (unsigned long long)exps); }
+}
+
+// Bulk-copy staged variant of K4a (tbeam.cuh).
+template <int NL, int CPL>
+__global__ void __launch_bounds__(128, 4) k_build_search_t(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize, uint32_t stage_rows,
+                                                           unsigned long long* counters) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
+    WarpSmem S; WarpStage T;
+    carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
+    uint32_t evals = 0, exps = 0;
+    for (uint32_t it = blockIdx.x * wpb + warp; it < b.count; it += gridDim.x * wpb) {
+        const uint32_t slot = b.first_slot + it;
+        int lvl = 0;
+        while (lvl + 1 <= b.new_top && slot % g.stride[lvl + 1] == 0) ++lvl;
+        for (int l = 0; l <= lvl; ++l) {
+            const uint32_t idx = slot / g.stride[l] - b.first_row[l];
+            if (lane == 0) b.cand_n[l][idx] = 0;
+        }
+        if (g.n_slots == 0) continue;
+        const float qn = warp_load_row(g, S.q4, slot);
+        QRegs<CPL> Q; Q.load(S.q4);
+        uint32_t cur = 0; float dcur = stage_entry_dist<CPL>(g, S, T, Q, qn, 0u, evals);
+        for (int l = g.top_level; l > lvl; --l) tgreedy_level<CPL>(g, l, S, T, Q, qn, cur, dcur, evals, exps);
+        RList<NL> L;
+        rbeam_seed(S, L, (int)ef, cur, dcur);
+        for (int l = min(lvl, g.top_level); l >= 0; --l) {
+            tbeam_level<NL, CPL>(g, l, S, T, Q, L, qn, evals, exps);
             const uint32_t idx = slot / g.stride[l] - b.first_row[l];
             uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
             uint32_t n = 0;
@@ -222,7 +313,7 @@ __device__ __forceinline__ bool heuristic_try(const GraphView& g, WarpSmem& S, K
 // reverse edge (kept -> item) with the inbox of the kept node's row.
 __global__ void __launch_bounds__(128) k_select(GraphView g, BuildBatch b, LinkTables t, uint32_t efp, uint32_t kbp,
                                                 unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, 32, 32);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 32, 32, 32);
@@ -280,7 +371,7 @@ __global__ void k_inbox_fill(LinkTables t) {
 // One warp per touched row: candidates = current row + inbox; if they fit the row they are
 // appended (sorted by distance), otherwise the heuristic re-prunes to the row cap.
 __global__ void __launch_bounds__(128) k_reverse_merge(GraphView g, LinkTables t, unsigned long long* counters) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, 64, 32);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 64, 64, 32);
@@ -402,6 +493,60 @@ static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t s
     return p;
 }
 
+
+// ---- staged (bulk-copy) launch geometry: per-warp staging budget -> rows per round ----
+static inline uint32_t stage_rows_for(const GraphView& g, const DeviceInfo& dev) {
+    const uint32_t row_bytes = g.dpad * 4;
+    uint32_t rows = dev.stage_bytes / row_bytes;
+    if (rows > 32) rows = 32;
+    if (rows < 2) rows = 2;
+    return rows;
+}
+static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev) {
+    uint32_t hs = next_pow2(ef * dev.hash_factor);
+    if (hs < 1024) hs = 1024;
+    if (hs > 16384) hs = 16384;
+    return hs;
+}
+
+template <int NL, int CPL>
+static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                                   uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev), wpb = 4;
+    const size_t smem = tsmem_bytes(g.dpad, hs, rows) * wpb;
+    if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_search_t<NL, CPL><<<(nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters);
+    return cudaGetLastError();
+}
+template <int NL>
+static cudaError_t launch_search_tc(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    if (g.chunks == 32) return launch_search_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+    if (g.chunks == 24) return launch_search_t<NL, 3>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+    return launch_search_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+}
+
+template <int NL, int CPL>
+static cudaError_t launch_build_search_t(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
+                                         unsigned long long* counters, cudaStream_t st) {
+    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev), wpb = 4;
+    const size_t smem = tsmem_bytes(g.dpad, hs, rows) * wpb;
+    if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_build_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_build_search_t<NL, CPL><<<(b.count + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, b, ef, build_efp(ef), hs, rows, counters);
+    return cudaGetLastError();
+}
+template <int NL>
+static cudaError_t launch_build_search_tc(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
+                                          unsigned long long* counters, cudaStream_t st) {
+    if (g.chunks == 32) return launch_build_search_t<NL, 4>(g, b, ef, dev, counters, st);
+    if (g.chunks == 24) return launch_build_search_t<NL, 3>(g, b, ef, dev, counters, st);
+    return launch_build_search_t<NL, 0>(g, b, ef, dev, counters, st);
+}
+
 template <int NL>
 static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
@@ -420,6 +565,14 @@ static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, u
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                           uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
     if (nq == 0) return cudaSuccess;
+    if (dev.stage_bytes && !dev.force_smem_list && ef <= 256) {
+        cudaError_t e;
+        if (ef <= 32) e = launch_search_tc<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 64) e = launch_search_tc<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 128) e = launch_search_tc<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else e = launch_search_tc<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (e != cudaErrorInvalidConfiguration) return e;   // rows too long for the staging area: register-gather kernels below
+    }
     if (!dev.force_smem_list) {
         if (ef <= 32) return launch_search_r<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
         if (ef <= 64) return launch_search_r<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
@@ -455,6 +608,14 @@ static cudaError_t launch_build_search_r(const GraphView& g, const BuildBatch& b
 cudaError_t launch_build_search(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
                                 unsigned long long* counters, cudaStream_t st) {
     if (b.count == 0) return cudaSuccess;
+    if (dev.stage_bytes && !dev.force_smem_list && ef <= 256) {
+        cudaError_t e;
+        if (ef <= 32) e = launch_build_search_tc<1>(g, b, ef, dev, counters, st);
+        else if (ef <= 64) e = launch_build_search_tc<2>(g, b, ef, dev, counters, st);
+        else if (ef <= 128) e = launch_build_search_tc<4>(g, b, ef, dev, counters, st);
+        else e = launch_build_search_tc<8>(g, b, ef, dev, counters, st);
+        if (e != cudaErrorInvalidConfiguration) return e;
+    }
     if (!dev.force_smem_list) {
         if (ef <= 32) return launch_build_search_r<1>(g, b, ef, dev, counters, st);
         if (ef <= 64) return launch_build_search_r<2>(g, b, ef, dev, counters, st);

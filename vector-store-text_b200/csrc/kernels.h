@@ -13,8 +13,9 @@ struct DeviceInfo {
     int device = 0;
     int sm_count = 148;
     size_t smem_per_block = 227 * 1024;
-    uint32_t hash_factor = 16;
-    bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
+    uint32_t hash_factor = 16;         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
+    bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)
+    uint32_t stage_bytes = 8192;       // per-warp bulk-copy staging area (VSANN_STAGE_BYTES; 0 = register-gather kernels)
 };
 
 struct SearchPlan { uint32_t efp, hsize, warps_per_block, blocks_per_sm; size_t smem; };

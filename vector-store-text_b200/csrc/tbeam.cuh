@@ -1,0 +1,232 @@
+// tbeam.cuh — bulk-copy (TMA) staged gathers for the warp beam.
+//
+// Same traversal as rbeam.cuh (reference: usearch::Index::search / add, src/index/usearch.rs:276,221),
+// but the neighbour vectors of one expansion are fetched by ONE round of `cp.async.bulk`
+// (global -> shared, one row per lane, completion on a per-warp mbarrier) instead of four
+// dependent rounds of register loads: a warp keeps up to `rows` x row_bytes in flight without
+// holding them in registers, so a beam step costs two dependent memory round trips (link row,
+// then all vectors) and the link row of every accepted candidate is prefetched into L2 as soon
+// as it is accepted. Distances use the accumulation order of warp_dist32 (8-lane teams, chunk
+// c = tl + 8 i, xor-4/2/1 reduction), so both paths return identical bits.
+#pragma once
+#include "rbeam.cuh"
+
+namespace vsann {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+// global -> shared bulk copy (bytes % 16 == 0, both addresses 16 B aligned), completes on `bar`
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+#ifndef VSANN_NO_PREFETCH
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
+}
+
+struct WarpStage {
+    const unsigned char* buf;   // rows x row_bytes staging area (generic pointer)
+    uint32_t buf_s;             // its shared-space address
+    uint32_t bar;               // shared-space address of the warp's mbarrier
+    uint32_t parity;            // parity of the next completion
+    uint32_t rows;              // staging capacity in rows
+    uint32_t row_bytes;         // dpad * 4
+};
+
+// per-warp layout: query | scr_id[32] | scr_d[32] | mbarrier (16 B) | visited hash | staging rows (128 B aligned)
+__host__ __device__ inline size_t tsmem_bytes(uint32_t dpad, uint32_t hsize, uint32_t rows) {
+    size_t b = (size_t)dpad * 4 + 256 + 16 + (size_t)hsize * 4;
+    b = (b + 127) & ~(size_t)127;
+    return b + (size_t)rows * dpad * 4;
+}
+
+__device__ __forceinline__ void carve_tsmem(unsigned char* base, uint32_t dpad, uint32_t hsize, uint32_t rows, WarpSmem& S, WarpStage& T) {
+    unsigned char* p = base;
+    S.q4 = reinterpret_cast<float4*>(p); p += (size_t)dpad * 4;
+    S.scr_id = reinterpret_cast<uint32_t*>(p); p += 128;
+    S.scr_d = reinterpret_cast<float*>(p); p += 128;
+    T.bar = smem_u32(p); p += 16;
+    S.hs = reinterpret_cast<uint32_t*>(p); p += (size_t)hsize * 4;
+    S.hmask = hsize - 1;
+    p = base + ((((size_t)(p - base)) + 127) & ~(size_t)127);
+    T.buf = p; T.buf_s = smem_u32(p);
+    T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0;
+    S.L.ld = S.L.ld2 = nullptr; S.L.li = S.L.li2 = nullptr; S.L.cap = S.L.capp = 0;
+    if (lane_id() == 0) mbar_init(T.bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+}
+
+// Query chunks a lane owns in the team layout: c = tl + 8 i. CPL == 0: read them from shared memory.
+template <int CPL>
+struct QRegs {
+    float4 v[CPL > 0 ? CPL : 1];
+    __device__ __forceinline__ void load(const float4* q4) {
+        const unsigned tl = lane_id() & 7u;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) v[i] = q4[tl + 8 * i];
+    }
+};
+
+template <int METRIC>
+__device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, float& acc) {
+    if (METRIC == L2SQ) {
+        float t;
+        t = q.x - x.x; acc = fmaf(t, t, acc); t = q.y - x.y; acc = fmaf(t, t, acc);
+        t = q.z - x.z; acc = fmaf(t, t, acc); t = q.w - x.w; acc = fmaf(t, t, acc);
+    } else {
+        acc = fmaf(q.x, x.x, acc); acc = fmaf(q.y, x.y, acc);
+        acc = fmaf(q.z, x.z, acc); acc = fmaf(q.w, x.w, acc);
+    }
+}
+
+// Distances from the warp's query to up to 32 rows, one id per lane (NONE = skip); +inf for skipped lanes.
+template <int METRIC, int CPL>
+__device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
+                                                uint32_t id, uint32_t& n_evals) {
+    const unsigned lane = lane_id(), team = lane >> 3, tl = lane & 7u;
+    const unsigned valid = __ballot_sync(0xffffffffu, id != NONE);
+    if (valid == 0u) return INFINITY;
+    const int nvalid = __popc(valid);
+    const int pos = __popc(valid & ((1u << lane) - 1u));
+    if (id != NONE) S.scr_id[pos] = id;
+    __syncwarp();
+    n_evals += nvalid;
+    const int chunks = g.chunks;
+    for (int base = 0; base < nvalid; base += (int)T.rows) {
+        const int n = min((int)T.rows, nvalid - base);
+        if (lane == 0) mbar_arrive_expect_tx(T.bar, (uint32_t)n * T.row_bytes);
+        float vn = 0.f;
+        if ((int)lane < n) {
+            const uint32_t rid = S.scr_id[base + lane];
+            bulk_g2s(T.buf_s + lane * T.row_bytes, g.vecs + (size_t)rid * g.dpad, T.row_bytes, T.bar);
+            if (METRIC == COS) vn = g.sqn[rid];
+        }
+        mbar_wait(T.bar, T.parity); T.parity ^= 1u;
+        if (METRIC == COS) { if ((int)lane < n) S.scr_d[base + lane] = vn; __syncwarp(); }
+        for (int jb = 0; jb < n; jb += 8) {   // warp-uniform trip count: the shuffles below need every lane
+            const int j0 = jb + (int)team, j1 = j0 + 4;
+            const bool one = j0 < n, two = j1 < n;
+            const float4* xa = reinterpret_cast<const float4*>(T.buf + (size_t)(one ? j0 : 0) * T.row_bytes);
+            const float4* xb = reinterpret_cast<const float4*>(T.buf + (size_t)(two ? j1 : 0) * T.row_bytes);
+            float acc_a = 0.f, acc_b = 0.f;
+            if (CPL > 0) {
+#pragma unroll
+                for (int i = 0; i < CPL; ++i) {
+                    const float4 x = xa[tl + 8 * i], y = xb[tl + 8 * i];
+                    acc_chunk<METRIC>(Q.v[i], x, acc_a); acc_chunk<METRIC>(Q.v[i], y, acc_b);
+                }
+            } else {
+#pragma unroll 4
+                for (int c = tl; c < chunks; c += 8) {
+                    const float4 x = xa[c], y = xb[c], q = S.q4[c];
+                    acc_chunk<METRIC>(q, x, acc_a); acc_chunk<METRIC>(q, y, acc_b);
+                }
+            }
+#pragma unroll
+            for (int o = 4; o >= 1; o >>= 1) {
+                acc_a += __shfl_xor_sync(0xffffffffu, acc_a, o);
+                acc_b += __shfl_xor_sync(0xffffffffu, acc_b, o);
+            }
+            if (tl == 0) {
+                if (one) S.scr_d[base + j0] = finish_metric(METRIC, acc_a, qn, METRIC == COS ? S.scr_d[base + j0] : 0.f);
+                if (two) S.scr_d[base + j1] = finish_metric(METRIC, acc_b, qn, METRIC == COS ? S.scr_d[base + j1] : 0.f);
+            }
+        }
+        __syncwarp();   // staging rows are free again, distances visible
+    }
+    const float d = id != NONE ? S.scr_d[pos] : INFINITY;
+    __syncwarp();
+    return d;
+}
+
+template <int CPL>
+__device__ __forceinline__ float stage_dist32(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
+                                              uint32_t id, uint32_t& n_evals) {
+    switch (g.metric) {
+        case L2SQ: return stage_dist32_m<L2SQ, CPL>(g, S, T, Q, qn, id, n_evals);
+        case IP: return stage_dist32_m<IP, CPL>(g, S, T, Q, qn, id, n_evals);
+        default: return stage_dist32_m<COS, CPL>(g, S, T, Q, qn, id, n_evals);
+    }
+}
+
+template <int CPL>
+__device__ __forceinline__ float stage_entry_dist(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
+                                                  uint32_t entry, uint32_t& evals) {
+    const float d = stage_dist32<CPL>(g, S, T, Q, qn, lane_id() == 0 ? entry : NONE, evals);
+    return __shfl_sync(0xffffffffu, d, 0);
+}
+
+// Greedy 1-best walk on an upper level (cf. greedy_level in beam.cuh).
+template <int CPL>
+__device__ __forceinline__ void tgreedy_level(const GraphView& g, int level, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
+                                              uint32_t& cur, float& dcur, uint32_t& evals, uint32_t& exps) {
+    const unsigned lane = lane_id();
+    for (;;) {
+        int width; const uint32_t* row = level_row(g, level, cur, width);
+        ++exps;
+        float bd = INFINITY; uint32_t bi = NONE;
+        for (int off = 0; off < width; off += 32) {
+            uint32_t nb = (off + (int)lane < width) ? row[off + lane] : NONE;
+            if (nb != NONE && nb >= g.n_slots) nb = NONE;
+            const float d = stage_dist32<CPL>(g, S, T, Q, qn, nb, evals);
+            if (nb != NONE && pair_less(d, nb, bd, bi)) { bd = d; bi = nb; }
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (pair_less(od, oi, bd, bi)) { bd = od; bi = oi; }
+        }
+        if (bi != NONE && bd < dcur) {
+            cur = bi; dcur = bd;
+            int w2; prefetch_l2(level_row(g, level, cur, w2));
+        } else break;
+    }
+}
+
+// ef-wide beam on `level` with the register list (cf. rbeam_level).
+template <int NL, int CPL>
+__device__ __forceinline__ void tbeam_level(const GraphView& g, int level, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q,
+                                            RList<NL>& L, float qn, uint32_t& evals, uint32_t& exps) {
+    const unsigned lane = lane_id();
+    for (;;) {
+        float dc; const uint32_t c = L.pop(dc);
+        if (c == NONE) break;
+        ++exps;
+        int width; const uint32_t* row = level_row(g, level, c, width);
+        for (int off = 0; off < width; off += 32) {
+            uint32_t nb = (off + (int)lane < width) ? row[off + lane] : NONE;
+            if (nb != NONE && nb >= g.n_slots) nb = NONE;
+            if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+            __syncwarp();
+            const float d = stage_dist32<CPL>(g, S, T, Q, qn, nb, evals);
+            const bool good = nb != NONE && d < L.worst;
+            if (good) { int w2; prefetch_l2(level_row(g, level, nb, w2)); }   // it may be expanded later: have its links in L2
+            unsigned acc = __ballot_sync(0xffffffffu, good);
+            while (acc) {
+                const int src = __ffs(acc) - 1; acc &= acc - 1;
+                const float nd = __shfl_sync(0xffffffffu, d, src);
+                const uint32_t nid = __shfl_sync(0xffffffffu, nb, src);
+                if (nd < L.worst) L.insert(nd, nid);
+            }
+        }
+    }
+}
+
+}  // namespace vsann
