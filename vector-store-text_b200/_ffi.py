@@ -47,6 +47,8 @@ class VsError(RuntimeError):
 
 
 def lib_path() -> str:
+    if os.environ.get("VSANN_LIB"):          # developer hook: A/B a differently compiled libvsann.so
+        return os.environ["VSANN_LIB"]
     return os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libvsann.so")
 
 

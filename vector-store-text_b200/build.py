@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "lib", "libvsann.so")
+OUT = os.environ.get("VSANN_LIB_OUT") or os.path.join(HERE, "lib", "libvsann.so")
 SOURCES = ["index.cu", "graph_kernels.cu", "exact_kernels.cu"]
 HEADERS = ["common.cuh", "beam.cuh", "rbeam.cuh", "tbeam.cuh", "kernels.h", os.path.join("..", "..", "include", "vsann.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -4,8 +4,14 @@
 // Reference behaviour restated: usearch::Index::search (src/index/usearch.rs:276) and
 // usearch::Index::add (src/index/usearch.rs:221); algorithm per SURVEY.md Appendix B, CPU
 // restatement in oracle/oracle_vsann.cpp (hnsw_search / hnsw_insert / select_heuristic).
+#include <algorithm>
+#include <atomic>
 #include "tbeam.cuh"
 #include "kernels.h"
+
+#ifndef VSANN_T_MINB
+#define VSANN_T_MINB 6   // resident blocks per SM the staged kernels are compiled for
+#endif
 
 namespace vsann {
 
@@ -116,17 +122,21 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
 // Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
 // float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, 4) k_search_t(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+__global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                      uint32_t ef, uint32_t hsize, uint32_t stage_rows,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
-                                                     unsigned long long* counters) {
+                                                     unsigned long long* counters, uint32_t* work) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
     WarpSmem S; WarpStage T;
     carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
     uint32_t evals = 0, exps = 0, done = 0;
-    for (uint32_t q = blockIdx.x * wpb + warp; q < nq; q += gridDim.x * wpb) {
+    for (;;) {   // persistent warps: every warp draws its next query from a device counter (no tail, no intra-block wait)
+        uint32_t q = 0;
+        if (lane == 0) q = atomicAdd(work, 1u);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= nq) break;
         warp_load_query(S.q4, queries + (size_t)q * g.dims, g.dims, g.dpad);
         QRegs<CPL> Q; Q.load(S.q4);
         uint64_t* ko = keys_out + (size_t)q * k; float* dd = dist_out + (size_t)q * k;
@@ -248,15 +258,19 @@ __global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBat
 
 // Bulk-copy staged variant of K4a (tbeam.cuh).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, 4) k_build_search_t(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize, uint32_t stage_rows,
-                                                           unsigned long long* counters) {
+__global__ void __launch_bounds__(128, VSANN_T_MINB) k_build_search_t(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize, uint32_t stage_rows,
+                                                           unsigned long long* counters, uint32_t* work) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
     WarpSmem S; WarpStage T;
     carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
     uint32_t evals = 0, exps = 0;
-    for (uint32_t it = blockIdx.x * wpb + warp; it < b.count; it += gridDim.x * wpb) {
+    for (;;) {
+        uint32_t it = 0;
+        if (lane == 0) it = atomicAdd(work, 1u);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= b.count) break;
         const uint32_t slot = b.first_slot + it;
         int lvl = 0;
         while (lvl + 1 <= b.new_top && slot % g.stride[lvl + 1] == 0) ++lvl;
@@ -494,6 +508,14 @@ static SearchPlan plan_search(uint32_t dpad, uint32_t ef, int sm_count, size_t s
 }
 
 
+// Work counter of one persistent launch: a slot of the index's ring, zeroed in stream order.
+static std::atomic<uint32_t> g_work_next{0};
+static cudaError_t next_work_counter(const DeviceInfo& dev, cudaStream_t st, uint32_t** out) {
+    if (!dev.work_ring) return cudaErrorInvalidValue;
+    *out = dev.work_ring + (g_work_next.fetch_add(1) % WORK_RING_SLOTS);
+    return cudaMemsetAsync(*out, 0, sizeof(uint32_t), st);
+}
+
 // ---- staged (bulk-copy) launch geometry: per-warp staging budget -> rows per round ----
 static inline uint32_t stage_rows_for(const GraphView& g, const DeviceInfo& dev) {
     const uint32_t row_bytes = g.dpad * 4;
@@ -517,7 +539,10 @@ static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, u
     if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    k_search_t<NL, CPL><<<(nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters);
+    uint32_t* work = nullptr;
+    if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
+    const uint32_t blocks = std::min<uint32_t>((nq + wpb - 1) / wpb, (uint32_t)dev.sm_count * VSANN_T_MINB);
+    k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work);
     return cudaGetLastError();
 }
 template <int NL>
@@ -536,7 +561,10 @@ static cudaError_t launch_build_search_t(const GraphView& g, const BuildBatch& b
     if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_build_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    k_build_search_t<NL, CPL><<<(b.count + wpb - 1) / wpb, wpb * 32, smem, st>>>(g, b, ef, build_efp(ef), hs, rows, counters);
+    uint32_t* work = nullptr;
+    if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
+    const uint32_t blocks = std::min<uint32_t>((b.count + wpb - 1) / wpb, (uint32_t)dev.sm_count * VSANN_T_MINB);
+    k_build_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(g, b, ef, build_efp(ef), hs, rows, counters, work);
     return cudaGetLastError();
 }
 template <int NL>

@@ -344,6 +344,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
         CU(cudaEventCreate(&ix->ev0)); CU(cudaEventCreate(&ix->ev1)); CU(cudaEventCreateWithFlags(&ix->user_ev, cudaEventDisableTiming));
         CU(cudaMalloc(&ix->counters, 8 * sizeof(unsigned long long)));
         CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
+        CU(cudaMalloc(&ix->dev.work_ring, WORK_RING_SLOTS * sizeof(uint32_t)));
         vs_status r = do_reserve(ix, ix->reserve_increment); if (r != VS_OK) return r;
         r = setup_build_scratch(ix); if (r != VS_OK) return r;
         CU(cudaStreamSynchronize(ix->stream));
@@ -360,7 +361,7 @@ void vs_index_destroy(vs_index* ix) {
     if (ix->stream) cudaStreamSynchronize(ix->stream);
     cudaFree(ix->vecs); cudaFree(ix->sqn); cudaFree(ix->links0); cudaFree(ix->slot_key); cudaFree(ix->deleted);
     for (int l = 1; l < MAX_LEVELS; ++l) cudaFree(ix->linksU[l]);
-    cudaFree(ix->lt.inbox_cnt); cudaFree(ix->lt.inbox_idx); cudaFree(ix->counters);
+    cudaFree(ix->lt.inbox_cnt); cudaFree(ix->lt.inbox_idx); cudaFree(ix->counters); cudaFree(ix->dev.work_ring);
     ix->build_scratch.release(); ix->exact_scratch.release(); ix->stage.release(); ix->tomb.release();
     ix->qpad.release(); ix->qdense.release(); ix->out_d.release(); ix->out_k.release();
     if (ix->ev0) cudaEventDestroy(ix->ev0); if (ix->ev1) cudaEventDestroy(ix->ev1); if (ix->user_ev) cudaEventDestroy(ix->user_ev);

@@ -6,6 +6,7 @@
 
 namespace vsann {
 
+constexpr uint32_t WORK_RING_SLOTS = 256;
 constexpr uint32_t INBOX_CAP = 32;     // reverse edges one row can receive per batch
 constexpr uint32_t KNN_BATCH = 32;     // intra-batch exact neighbours merged into the candidates
 
@@ -15,7 +16,8 @@ struct DeviceInfo {
     size_t smem_per_block = 227 * 1024;
     uint32_t hash_factor = 16;         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
     bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)
-    uint32_t stage_bytes = 8192;       // per-warp bulk-copy staging area (VSANN_STAGE_BYTES; 0 = register-gather kernels)
+    uint32_t stage_bytes = 4096;       // per-warp bulk-copy staging area (VSANN_STAGE_BYTES; 0 = register-gather kernels)
+    uint32_t* work_ring = nullptr;     // WORK_RING_SLOTS device words: work counters of the persistent kernels
 };
 
 struct SearchPlan { uint32_t efp, hsize, warps_per_block, blocks_per_sm; size_t smem; };
