@@ -1,0 +1,529 @@
+// exact_tc.cu — K1 on the 5th-generation tensor cores: brute-force k-NN as a TF32 tcgen05 GEMM with
+// TMA-fed tiles and TMEM accumulators, followed by an exact FP32 re-rank (K2) so that the ids AND
+// the distance bits are those of the oracle's exact search (oracle/oracle_vsann.cpp exact_search;
+// "the reference's exact search", SURVEY.md §8c — usearch::Index::search at usearch.rs:276 run
+// exhaustively).
+//
+//   1. k_tc_scan<SAMPLE>  D = Q · X^T on every 32nd corpus tile; every query keeps its R smallest keys
+//   2. k_tc_threshold     tau[q] = r-th smallest sampled key  (expected |{x : key <= tau}| = 32 r >> k)
+//   3. k_tc_scan<EMIT>    full scan; (q, slot) pairs with key <= tau[q] are appended to cand[q][]
+//   4. k_tc_rerank        exact sequential-fmaf distance of every candidate, top-k by (distance, key);
+//                         proves the answer: every row that was NOT emitted has approximate distance
+//                         > tau, hence exact distance > tau - eps >= the k-th exact distance found
+//   5. queries whose proof fails (ties wider than eps, candidate overflow, < k live candidates) are
+//      answered by the FP32 tile kernel (exact_kernels.cu). There is no CPU path.
+//
+// key = a_j * dot + b_j with per-row (a_j, b_j): L2SQ (-2, |x|^2), IP (-1, 0), COS (-1/|x|, 0);
+// tombstoned rows and rows past the end get (0, +inf). dist = f(key) is monotone per query.
+//
+// CTA = 128 queries (UMMA M) x one corpus slice, tiles of 256 rows (UMMA N), K in blocks of 32 floats
+// (one 128 B swizzle row). Warps 0-3: epilogue (TMEM lane quarter = warp), warp 4: TMA producer,
+// warp 5: MMA issuer + TMEM allocator. 4-stage smem ring, 2 TMEM accumulators of 256 columns.
+#include <cuda.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include "common.cuh"
+#include "kernels.h"
+
+namespace vsann {
+namespace tc {
+
+constexpr int BM = 128, BN = 256, BK = 32, STAGES = 4, UMMA_K = 8;
+constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int THREADS = 192, EPI_THREADS = 128;
+constexpr int R_MAX = 16;              // sampled keys kept per (query, slice)
+constexpr int SAMPLE_STRIDE = 32;      // every 32nd tile is sampled
+constexpr uint32_t TMEM_COLS = 512;
+
+// dynamic shared memory (after rounding the base up to 1024 B)
+struct __align__(16) Ctrl {
+    unsigned long long full[STAGES], empty[STAGES], tfull[2], tempty[2];
+    uint32_t tmem_base;
+    uint32_t pad[3];
+};
+constexpr size_t COLV_BYTES = 2 * BN * sizeof(float2);
+constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + COLV_BYTES + sizeof(Ctrl);
+
+// ---- PTX wrappers --------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, FP32 accumulate; issued by ONE thread
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// mbarrier arrive once every MMA issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major operand tile, 128 B swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO), LBO unused (= 1).
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::tf32, FP32 accumulate, A and B K-major, M = 128, N = BN
+constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+
+// |q|^2 by the sequential fmaf chain of the oracle (same bits as k_query_norms / k_row_norms)
+__global__ void k_query_norms_tc(const float* __restrict__ q, size_t stride, uint32_t dpad, uint32_t nq, float* __restrict__ qn) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const float* v = q + (size_t)i * stride;
+    float acc = 0.f;
+    for (uint32_t c = 0; c < dpad; ++c) acc = fmaf(v[c], v[c], acc);
+    qn[i] = acc;
+}
+
+struct ScanArgs {
+    const float* sqn; const uint32_t* deleted;   // sqn by row, tombstones by slot (row r is slot first_slot + r)
+    uint32_t first_slot, n, nq, nq_pad, kblocks;
+    int metric;
+    uint32_t n_tiles, tiles_per_slice;
+    float* samp;                                 // SAMPLE: [slices][nq_pad][R_MAX] ascending
+    const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
+};
+
+// (a, b) of one corpus row: key = a * dot + b
+__device__ __forceinline__ float2 row_coeffs(const ScanArgs& a, uint32_t r) {
+    if (r >= a.n) return make_float2(0.f, INFINITY);
+    const uint32_t slot = a.first_slot + r;
+    if (a.deleted && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) return make_float2(0.f, INFINITY);
+    if (a.metric == L2SQ) return make_float2(-2.f, a.sqn[r]);
+    if (a.metric == IP) return make_float2(-1.f, 0.f);
+    const float xn = a.sqn[r];
+    return make_float2(xn > 0.f ? -rsqrtf(xn) : 0.f, 0.f);
+}
+
+template <bool EMIT>
+__global__ void __launch_bounds__(THREADS, 1)
+k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapX, const ScanArgs a) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float2* colv = reinterpret_cast<float2*>(smem + (size_t)STAGES * STAGE_BYTES);
+    Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem + (size_t)STAGES * STAGE_BYTES + COLV_BYTES);
+    const uint32_t smem_s = s32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t q0 = blockIdx.x * BM, slice = blockIdx.y;
+    const uint32_t t_begin = slice * a.tiles_per_slice, t_end = min(a.n_tiles, t_begin + a.tiles_per_slice);
+    const uint32_t t_step = EMIT ? 1u : (uint32_t)SAMPLE_STRIDE;
+    const uint32_t t_first = EMIT ? t_begin : ((t_begin + SAMPLE_STRIDE - 1) / SAMPLE_STRIDE) * SAMPLE_STRIDE;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&ctrl->tmem_base)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = ctrl->tmem_base;
+
+    if (warp == 4) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (uint32_t t = t_first; t < t_end; t += t_step) {
+                for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
+                    mbar_wait(s32(&ctrl->empty[stage]), phase ^ 1u);
+                    const uint32_t full = s32(&ctrl->full[stage]);
+                    mbar_expect_tx(full, STAGE_BYTES);
+                    const uint32_t dst = smem_s + stage * STAGE_BYTES;
+                    tma_load_2d(dst, &mapQ, full, (int)(kb * BK), (int)q0);
+                    tma_load_2d(dst + A_BYTES, &mapX, full, (int)(kb * BK), (int)(t * BN));
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0, it = 0;
+            for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
+                const uint32_t buf = it & 1u;
+                mbar_wait(s32(&ctrl->tempty[buf]), ((it >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * BN;
+                for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
+                    mbar_wait(s32(&ctrl->full[stage]), phase);
+                    tc_fence_after();
+                    const uint64_t da = smem_desc_sw128(smem_s + stage * STAGE_BYTES);
+                    const uint64_t db = smem_desc_sw128(smem_s + stage * STAGE_BYTES + A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_tf32(d_tmem, da + (uint64_t)(k * UMMA_K * 4 >> 4), db + (uint64_t)(k * UMMA_K * 4 >> 4), IDESC_TF32, (kb | (uint32_t)k) != 0u);
+                    umma_commit(s32(&ctrl->empty[stage]));      // frees the smem stage once these MMAs are done
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(s32(&ctrl->tfull[buf]));              // accumulator ready for the epilogue
+            }
+        }
+    } else {
+        // ===== epilogue: thread = one query row of the accumulator =====
+        const uint32_t row = threadIdx.x, q = q0 + row;
+        const bool qok = q < a.nq;
+        float tau = -INFINITY;
+        if (EMIT && qok) tau = a.tau[q];
+        float top[R_MAX];
+#pragma unroll
+        for (int i = 0; i < R_MAX; ++i) top[i] = INFINITY;
+        if (t_first < t_end) {
+            colv[row] = row_coeffs(a, t_first * BN + row);
+            colv[row + EPI_THREADS] = row_coeffs(a, t_first * BN + row + EPI_THREADS);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        uint32_t it = 0;
+        for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
+            const uint32_t buf = it & 1u, tn = t + t_step;
+            float2 n0 = make_float2(0.f, INFINITY), n1 = n0;
+            if (tn < t_end) { n0 = row_coeffs(a, tn * BN + row); n1 = row_coeffs(a, tn * BN + row + EPI_THREADS); }   // in flight during this tile
+            mbar_wait(s32(&ctrl->tfull[buf]), (it >> 1) & 1u);
+            tc_fence_after();
+            const float2* cv = colv + buf * BN;
+            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                float v[32];
+                tmem_ld32(taddr + c * 32, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float2 ab = cv[c * 32 + i];
+                    const float key = fmaf(ab.x, v[i], ab.y);
+                    if (EMIT) {
+                        if (key <= tau) {
+                            const uint32_t pos = atomicAdd(&a.cnt[q], 1u);
+                            if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + c * 32 + i;
+                        }
+                    } else if (key < top[R_MAX - 1]) {
+                        top[R_MAX - 1] = key;
+#pragma unroll
+                        for (int j = R_MAX - 1; j > 0; --j) {
+                            const float lo = fminf(top[j - 1], top[j]), hi = fmaxf(top[j - 1], top[j]);
+                            top[j - 1] = lo; top[j] = hi;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s32(&ctrl->tempty[buf]));
+            colv[(buf ^ 1u) * BN + row] = n0;
+            colv[(buf ^ 1u) * BN + row + EPI_THREADS] = n1;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+        if (!EMIT && qok) {
+            float* o = a.samp + ((size_t)slice * a.nq_pad + q) * R_MAX;
+#pragma unroll
+            for (int i = 0; i < R_MAX; ++i) o[i] = top[i];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+
+
+// tau[q] = r-th smallest of the keys sampled for q over all slices (one warp per query).
+__global__ void k_tc_threshold(const float* __restrict__ samp, uint32_t slices, uint32_t nq, uint32_t nq_pad, uint32_t r, float* __restrict__ tau) {
+    const uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (q >= nq) return;
+    const uint32_t total = slices * R_MAX;
+    float pv = -INFINITY; uint32_t pi = 0; bool have = false;
+    for (uint32_t round = 0; round < r; ++round) {
+        float bv = INFINITY; uint32_t bi = NONE;
+        for (uint32_t idx = lane; idx < total; idx += 32) {
+            const float v = samp[((size_t)(idx / R_MAX) * nq_pad + q) * R_MAX + (idx % R_MAX)];
+            const bool after = !have || v > pv || (v == pv && idx > pi);
+            if (after && (v < bv || (v == bv && idx < bi))) { bv = v; bi = idx; }
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (oi != NONE && (bi == NONE || ov < bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+        }
+        if (bi == NONE) { pv = INFINITY; break; }   // fewer than r samples: no usable threshold
+        pv = bv; pi = bi; have = true;
+    }
+    if (lane == 0) tau[q] = pv;
+}
+
+__global__ void k_tc_max_norm(const float* __restrict__ sqn, uint32_t n, uint32_t* out_bits) {
+    float m = 0.f;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = fmaxf(m, sqn[i]);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));   // non-negative floats order like their bits
+}
+
+// Worst-case |approximate distance - exact f32 distance| for one query (see the file header).
+__device__ __forceinline__ float tc_eps(int metric, float qn, float max_xn, uint32_t dpad) {
+    const float e_dot = 0.001953125f /* 2^-9: both operands truncated to TF32 */ + (float)dpad * 4.76837158e-7f /* d 2^-21: accumulation */;
+    const float e_f32 = (float)(dpad + 4) * 1.1920929e-7f;   // (d + 4) 2^-23: the two f32 chains
+    const float qx = sqrtf(qn) * sqrtf(max_xn);
+    float e;
+    if (metric == L2SQ) e = 2.f * qx * e_dot + (qn + max_xn) * e_f32 * 2.f;
+    else if (metric == IP) e = qx * (e_dot + e_f32);
+    else e = e_dot + e_f32 + 1e-6f;
+    return e * 1.25f;   // head-room for the rounding of this formula itself
+}
+
+struct RerankArgs {
+    const float* vecs; const float* sqn; const uint64_t* slot_key; const uint32_t* deleted;
+    uint32_t first_slot, n_slots, dpad;
+    const float* q; size_t q_stride; const float* qn; uint32_t nq;
+    int metric; uint32_t k, kp, cap;
+    const uint32_t* cand; const uint32_t* cnt; const float* tau; const uint32_t* max_xn_bits;
+    uint64_t* out_keys; float* out_dist;
+    uint32_t* n_flagged; uint32_t* flagged;      // queries the FP32 kernel must answer
+};
+
+// One warp per query: exact distances of the candidates (sequential fmaf chain over the dimensions,
+// exactly k_exact_tiles / the oracle), top-k by (distance, key), then the proof that no row outside
+// the candidate set can belong to the top-k.
+__global__ void __launch_bounds__(128) k_tc_rerank(RerankArgs a) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+    const uint32_t q = blockIdx.x * wpb + warp;
+    if (q >= a.nq) return;
+    const size_t per_warp = (size_t)a.dpad * 4 + 32 * 33 * 4 + (size_t)a.kp * 16 + 256;
+    unsigned char* base = sm + (size_t)warp * per_warp;
+    float* qs = reinterpret_cast<float*>(base); base += (size_t)a.dpad * 4;
+    float* tile = reinterpret_cast<float*>(base); base += 32 * 33 * 4;
+    SList L;
+    L.ld = reinterpret_cast<float*>(base); L.ld2 = L.ld + a.kp; L.li = reinterpret_cast<uint32_t*>(L.ld2 + a.kp); L.li2 = L.li + a.kp;
+    uint32_t* scr_id = L.li2 + a.kp; float* scr_d = reinterpret_cast<float*>(scr_id + 32);
+    L.cap = (int)a.k; L.capp = (int)a.kp;
+    slist_init(L);
+    for (uint32_t c = lane; c < a.dpad; c += 32) qs[c] = a.q[(size_t)q * a.q_stride + c];
+    __syncwarp();
+    const float qn = a.qn[q];
+    const uint32_t total = a.cnt[q];
+    const uint32_t cnt = min(total, a.cap);
+    const LessByKey less{a.slot_key, a.n_slots};
+    for (uint32_t b0 = 0; b0 < cnt; b0 += 32) {
+        uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
+        if (slot != NONE && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
+        float acc = 0.f;
+        for (uint32_t kc = 0; kc < a.dpad; kc += 32) {
+            // coalesced: all lanes read 32 consecutive floats of one candidate row, 32 rows in turn
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {
+                const uint32_t sj = __shfl_sync(0xffffffffu, slot, j);
+                float x = 0.f;
+                if (sj != NONE && kc + lane < a.dpad) x = __ldg(a.vecs + (size_t)(sj - a.first_slot) * a.dpad + kc + lane);
+                tile[j * 33 + lane] = x;
+            }
+            __syncwarp();
+            const uint32_t kend = min(32u, a.dpad - kc);
+            if (a.metric == L2SQ) { for (uint32_t i = 0; i < kend; ++i) { const float d = qs[kc + i] - tile[lane * 33 + i]; acc = fmaf(d, d, acc); } }
+            else { for (uint32_t i = 0; i < kend; ++i) acc = fmaf(qs[kc + i], tile[lane * 33 + i], acc); }
+            __syncwarp();
+        }
+        float d = INFINITY;
+        if (slot != NONE) d = finish_metric(a.metric, acc, qn, a.metric == COS ? a.sqn[slot - a.first_slot] : 0.f);
+        slist_merge(L, d, slot, scr_id, scr_d, less);
+    }
+    // proof: rows that were not emitted have key > tau  =>  exact distance > dist(tau) - eps
+    const float tau = a.tau[q], max_xn = __uint_as_float(*a.max_xn_bits);
+    float tau_dist;
+    if (a.metric == L2SQ) tau_dist = qn + tau;
+    else if (a.metric == IP) tau_dist = 1.f + tau;
+    else tau_dist = qn > 0.f ? 1.f + tau * rsqrtf(qn) : -INFINITY;
+    const float dk = L.ld[a.k - 1];
+    const bool full = L.li[a.k - 1] != NONE;
+    const bool proven = total <= a.cap && full && dk < tau_dist - tc_eps(a.metric, qn, max_xn, a.dpad);
+    if (proven) {
+        for (uint32_t i = lane; i < a.k; i += 32) {
+            const uint32_t id = L.li[i];
+            a.out_keys[(size_t)q * a.k + i] = a.slot_key[id];
+            a.out_dist[(size_t)q * a.k + i] = L.ld[i];
+        }
+    } else if (lane == 0) {
+        a.flagged[atomicAdd(a.n_flagged, 1u)] = q;
+    }
+}
+
+// gather / scatter for the queries that go to the FP32 kernel
+__global__ void k_tc_gather_queries(const float* __restrict__ q, size_t q_stride, uint32_t dpad, const uint32_t* __restrict__ flagged, uint32_t nf, float* __restrict__ out) {
+    const size_t total = (size_t)nf * dpad;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = q[(size_t)flagged[i / dpad] * q_stride + (i % dpad)];
+}
+__global__ void k_tc_scatter_results(const uint64_t* __restrict__ keys, const float* __restrict__ dist, uint32_t k, const uint32_t* __restrict__ flagged, uint32_t nf,
+                                     uint64_t* __restrict__ out_keys, float* __restrict__ out_dist) {
+    const size_t total = (size_t)nf * k;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t o = (size_t)flagged[i / k] * k + (i % k);
+        out_keys[o] = keys[i]; out_dist[o] = dist[i];
+    }
+}
+
+
+// ---- host side ---------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr; cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+// rows x dpad f32 matrix, row-major; box = box_rows x 32 floats, 128 B swizzle, zero fill outside
+static bool make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t dpad, size_t row_stride_floats, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {dpad, rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)row_stride_floats * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, kblocks, r, cap, kp; };
+
+static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
+    Plan p;
+    p.nqt = (nq + BM - 1) / BM; p.nq_pad = p.nqt * BM;
+    p.n_tiles = (n + BN - 1) / BN;
+    p.kblocks = (dpad + BK - 1) / BK;
+    uint32_t want = (8u * (uint32_t)sm_count + p.nqt - 1) / p.nqt;          // ~8 waves of CTAs
+    want = std::min<uint32_t>(want, std::max<uint32_t>(1u, p.n_tiles / 8));   // >= 8 tiles per CTA
+    want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 64u));
+    p.tiles_per_slice = (p.n_tiles + want - 1) / want;
+    p.slices = (p.n_tiles + p.tiles_per_slice - 1) / p.tiles_per_slice;
+    const float lam = (float)k / SAMPLE_STRIDE;
+    p.r = std::min<uint32_t>(R_MAX, (uint32_t)std::ceil(lam + 4.f * std::sqrt(lam) + 3.5f));
+    uint32_t cap = 1; while (cap < 4u * p.r * SAMPLE_STRIDE) cap <<= 1;
+    p.cap = cap;
+    p.kp = (k + 31u) & ~31u;
+    return p;
+}
+
+static inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+}  // namespace tc
+
+bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k) {
+    static const int mode = [] { const char* e = getenv("VSANN_EXACT_TC"); return e ? atoi(e) : -1; }();   // 0 off, 1 force, default auto
+    if (mode == 0) return false;
+    if (c.row_step != 1 || !c.slot_key || !c.deleted || q.self_step != 0 || k == 0 || k > 128) return false;
+    if (q.stride != q.dpad || c.row_stride != q.dpad || c.n < 2 * (uint32_t)tc::BN * tc::SAMPLE_STRIDE) return false;
+    if (mode == 1) return true;
+    return (uint64_t)c.n * q.nq >= (1ull << 24);
+}
+
+size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
+    const tc::Plan p = tc::make_plan(nq, n, k, dpad, sm_count);
+    using tc::al256;
+    return al256((size_t)nq * 4) * 3 + al256((size_t)p.slices * p.nq_pad * tc::R_MAX * 4) + al256((size_t)nq * p.cap * 4) +
+           al256((size_t)(nq + 2) * 4) + 512;
+}
+
+// Exact top-k of every query; results are those of launch_exact (FP32 kernel) bit for bit.
+// fb_scratch: scratch of the FP32 kernel, sized for nq queries. stats (host, optional): [0] += queries, [1] += queries sent to the FP32 kernel.
+cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint64_t* out_keys, float* out_dist,
+                            const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats) {
+    using namespace tc;
+    if (q.nq == 0) return cudaSuccess;
+    const Plan p = make_plan(q.nq, c.n, k, q.dpad, dev.sm_count);
+    if (scratch.bytes < exact_tc_scratch_bytes(q.nq, c.n, k, q.dpad, dev.sm_count)) return cudaErrorInvalidValue;
+    unsigned char* sp = (unsigned char*)scratch.ptr;
+    float* qn = (float*)sp; sp += al256((size_t)q.nq * 4);
+    float* tau = (float*)sp; sp += al256((size_t)q.nq * 4);
+    uint32_t* cnt = (uint32_t*)sp; sp += al256((size_t)q.nq * 4);
+    float* samp = (float*)sp; sp += al256((size_t)p.slices * p.nq_pad * R_MAX * 4);
+    uint32_t* cand = (uint32_t*)sp; sp += al256((size_t)q.nq * p.cap * 4);
+    uint32_t* flag = (uint32_t*)sp;   // [0] n_flagged, [1] max |x|^2 bits, [2..] flagged queries
+    CUtensorMap mapQ, mapX;
+    if (!make_map(&mapQ, q.q, q.nq, q.dpad, q.stride, BM) || !make_map(&mapX, c.vecs, c.n, q.dpad, c.row_stride, BN)) return cudaErrorNotSupported;
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_tc_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_tc_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(cnt, 0, (size_t)q.nq * 4, st)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(flag, 0, 8, st)) != cudaSuccess) return e;
+    k_query_norms_tc<<<(q.nq + 127) / 128, 128, 0, st>>>(q.q, q.stride, q.dpad, q.nq, qn);
+    k_tc_max_norm<<<dev.sm_count, 256, 0, st>>>(c.sqn, c.n, flag + 1);
+    ScanArgs a{};
+    a.sqn = c.sqn; a.deleted = c.deleted; a.first_slot = c.first_slot; a.n = c.n; a.nq = q.nq; a.nq_pad = p.nq_pad; a.kblocks = p.kblocks;
+    a.metric = metric; a.n_tiles = p.n_tiles; a.tiles_per_slice = p.tiles_per_slice;
+    a.samp = samp; a.tau = tau; a.cand = cand; a.cnt = cnt; a.cap = p.cap;
+    const dim3 grid(p.nqt, p.slices);
+    k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
+    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(samp, p.slices, q.nq, p.nq_pad, p.r, tau);
+    k_tc_scan<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
+    RerankArgs r{};
+    r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
+    r.q = q.q; r.q_stride = q.stride; r.qn = qn; r.nq = q.nq; r.metric = metric; r.k = k; r.kp = p.kp; r.cap = p.cap;
+    r.cand = cand; r.cnt = cnt; r.tau = tau; r.max_xn_bits = flag + 1; r.out_keys = out_keys; r.out_dist = out_dist;
+    r.n_flagged = flag; r.flagged = flag + 2;
+    const uint32_t wpb = 4; const size_t rsmem = (size_t)wpb * ((size_t)q.dpad * 4 + 32 * 33 * 4 + (size_t)p.kp * 16 + 256);
+    if (rsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    if ((e = cudaFuncSetAttribute(k_tc_rerank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem)) != cudaSuccess) return e;
+    k_tc_rerank<<<(q.nq + wpb - 1) / wpb, wpb * 32, rsmem, st>>>(r);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    uint32_t nf = 0;
+    if ((e = cudaMemcpyAsync(&nf, flag, 4, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    if (stats) { stats[0] += q.nq; stats[1] += nf; }
+    if (nf == 0) return cudaSuccess;
+    // unproven queries: FP32 tile kernel on the gathered subset
+    float* gq = nullptr; uint64_t* gk = nullptr; float* gd = nullptr;
+    if ((e = cudaMalloc(&gq, (size_t)nf * q.dpad * 4)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&gk, (size_t)nf * k * 8)) != cudaSuccess) { cudaFree(gq); return e; }
+    if ((e = cudaMalloc(&gd, (size_t)nf * k * 4)) != cudaSuccess) { cudaFree(gq); cudaFree(gk); return e; }
+    k_tc_gather_queries<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, flag + 2, nf, gq);
+    ExactQueries sub = q; sub.q = gq; sub.stride = q.dpad; sub.nq = nf;
+    e = launch_exact(c, sub, metric, k, k, nullptr, gk, gd, fb_scratch, dev, st);
+    if (e == cudaSuccess) {
+        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, k, flag + 2, nf, out_keys, out_dist);
+        e = cudaGetLastError();
+    }
+    cudaError_t e2 = cudaStreamSynchronize(st);
+    cudaFree(gq); cudaFree(gk); cudaFree(gd);
+    return e != cudaSuccess ? e : e2;
+}
+
+}  // namespace vsann

@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, stage;
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[2] = {0, 0};
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -293,6 +293,13 @@ vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t
         c.deleted = ix->deleted; c.slot_key = ix->slot_key; c.n_slots = ix->n_slots;
         ExactQueries q{}; q.q = ix->qpad.p; q.stride = ix->dpad; q.nq = (uint32_t)nq; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = 0; q.self_step = 0;
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
+        if (exact_tc_supported(c, q, (uint32_t)k)) {
+            // tcgen05 TF32 scan + exact FP32 re-rank (exact_tc.cu); same ids and distance bits as the FP32 kernel
+            CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes((uint32_t)nq, c.n, (uint32_t)k, ix->dpad, ix->dev.sm_count)));
+            ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
+            CU(launch_exact_tc(c, q, ix->metric, (uint32_t)k, d_keys, d_dist, ts, sc, ix->dev, st, ix->tc_stats));
+            return VS_OK;
+        }
         CU(launch_exact(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, sc, ix->dev, st));
         return VS_OK;
     }
@@ -362,7 +369,7 @@ void vs_index_destroy(vs_index* ix) {
     cudaFree(ix->vecs); cudaFree(ix->sqn); cudaFree(ix->links0); cudaFree(ix->slot_key); cudaFree(ix->deleted);
     for (int l = 1; l < MAX_LEVELS; ++l) cudaFree(ix->linksU[l]);
     cudaFree(ix->lt.inbox_cnt); cudaFree(ix->lt.inbox_idx); cudaFree(ix->counters); cudaFree(ix->dev.work_ring);
-    ix->build_scratch.release(); ix->exact_scratch.release(); ix->stage.release(); ix->tomb.release();
+    ix->build_scratch.release(); ix->exact_scratch.release(); ix->tc_scratch.release(); ix->stage.release(); ix->tomb.release();
     ix->qpad.release(); ix->qdense.release(); ix->out_d.release(); ix->out_k.release();
     if (ix->ev0) cudaEventDestroy(ix->ev0); if (ix->ev1) cudaEventDestroy(ix->ev1); if (ix->user_ev) cudaEventDestroy(ix->user_ev);
     if (ix->stream) cudaStreamDestroy(ix->stream);
@@ -484,6 +491,7 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->build_vectors = ix->st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = ix->st_build_batches;
     o->build_seconds = ix->st_build_seconds; o->device_bytes = ix->device_bytes + ix->build_scratch.n + ix->exact_scratch.n;
     o->top_level = (uint32_t)ix->top_level;
+    o->exact_tc_queries = ix->tc_stats[0]; o->exact_tc_fallback = ix->tc_stats[1];
     return VS_OK;
 }
 vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; return VS_OK; }
@@ -493,7 +501,7 @@ vs_status vs_reset_stats(vs_index* ix) {
     cudaSetDevice(ix->dev.device);
     CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
-    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0;
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->tc_stats[0] = ix->tc_stats[1] = 0;
     return VS_OK;
 }
 
