@@ -79,7 +79,8 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+// issue a 32-column load of this thread's accumulator row; tmem_wait() before the registers are read
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, float (&v)[32]) {
     uint32_t* r = reinterpret_cast<uint32_t*>(v);
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
                  "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
@@ -88,8 +89,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
                    "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
                    "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
                  : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major operand tile, 128 B swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO), LBO unused (= 1).
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
@@ -133,7 +134,8 @@ template <bool EMIT>
 __global__ void __launch_bounds__(THREADS, 1)
 k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapX, const ScanArgs a) {
     extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // round the base up to 1024 B (128 B swizzle atoms) by pointer arithmetic, so the compiler keeps the shared address space
+    unsigned char* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
     float2* colv = reinterpret_cast<float2*>(smem + (size_t)STAGES * STAGE_BYTES);
     Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem + (size_t)STAGES * STAGE_BYTES + COLV_BYTES);
     const uint32_t smem_s = s32(smem);
@@ -187,8 +189,12 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                     tc_fence_after();
                     const uint64_t da = smem_desc_sw128(smem_s + stage * STAGE_BYTES);
                     const uint64_t db = smem_desc_sw128(smem_s + stage * STAGE_BYTES + A_BYTES);
+#ifndef TC_DEBUG_SKIP_MMA
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
+#else
+                    if (kb == 0xffffffffu) for (int k = 0; k < 1; ++k)
+#endif
                         umma_tf32(d_tmem, da + (uint64_t)(k * UMMA_K * 4 >> 4), db + (uint64_t)(k * UMMA_K * 4 >> 4), IDESC_TF32, (kb | (uint32_t)k) != 0u);
                     umma_commit(s32(&ctrl->empty[stage]));      // frees the smem stage once these MMAs are done
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -219,29 +225,51 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
             tc_fence_after();
             const float2* cv = colv + buf * BN;
             const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BN;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                float v[32];
-                tmem_ld32(taddr + c * 32, v);
+            // Hot loop: key = a * dot + b and a running minimum, branch-free; the (rare) chunks whose minimum passes
+            // the bound are re-scanned element by element. The next 32 columns are in flight while these are processed.
+            const float4* cv4 = reinterpret_cast<const float4*>(cv);
+            auto process = [&](const float (&v)[32], int c) {
+                float mn = INFINITY;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float2 ab = cv[c * 32 + i];
-                    const float key = fmaf(ab.x, v[i], ab.y);
-                    if (EMIT) {
-                        if (key <= tau) {
-                            const uint32_t pos = atomicAdd(&a.cnt[q], 1u);
-                            if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + c * 32 + i;
-                        }
-                    } else if (key < top[R_MAX - 1]) {
-                        top[R_MAX - 1] = key;
+                for (int i = 0; i < 32; i += 2) {
+                    const float4 ab = cv4[(c * 32 + i) >> 1];
+                    mn = fminf(mn, fminf(fmaf(ab.x, v[i], ab.y), fmaf(ab.z, v[i + 1], ab.w)));
+                }
+                const float bound = EMIT ? tau : top[R_MAX - 1];
+                if (EMIT ? (mn <= bound) : (mn < bound)) {
 #pragma unroll
-                        for (int j = R_MAX - 1; j > 0; --j) {
-                            const float lo = fminf(top[j - 1], top[j]), hi = fmaxf(top[j - 1], top[j]);
-                            top[j - 1] = lo; top[j] = hi;
+                    for (int i = 0; i < 32; ++i) {   // unrolled: v[] stays in registers
+                        const float2 ab = cv[c * 32 + i];
+                        const float key = fmaf(ab.x, v[i], ab.y);
+                        if (EMIT) {
+                            if (key <= tau) {
+                                const uint32_t pos = atomicAdd(&a.cnt[q], 1u);
+                                if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + c * 32 + i;
+                            }
+                        } else if (key < top[R_MAX - 1]) {
+                            top[R_MAX - 1] = key;
+#pragma unroll
+                            for (int j = R_MAX - 1; j > 0; --j) {
+                                const float lo = fminf(top[j - 1], top[j]), hi = fmaxf(top[j - 1], top[j]);
+                                top[j - 1] = lo; top[j] = hi;
+                            }
                         }
                     }
                 }
+            };
+#ifndef TC_DEBUG_SKIP_EPI
+            float va[32], vb[32];
+            tmem_ld32_issue(taddr, va);
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c += 2) {
+                tmem_wait();
+                tmem_ld32_issue(taddr + (c + 1) * 32, vb);
+                process(va, c);
+                tmem_wait();
+                if (c + 2 < BN / 32) tmem_ld32_issue(taddr + (c + 2) * 32, va);
+                process(vb, c + 1);
             }
+#endif
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s32(&ctrl->tempty[buf]));
