@@ -17,8 +17,8 @@
 // tombstoned rows and rows past the end get (0, +inf). dist = f(key) is monotone per query.
 //
 // CTA = 128 queries (UMMA M) x one corpus slice, tiles of 256 rows (UMMA N), K in blocks of 32 floats
-// (one 128 B swizzle row). Warps 0-3: epilogue (TMEM lane quarter = warp), warp 4: TMA producer,
-// warp 5: MMA issuer + TMEM allocator. 4-stage smem ring, 2 TMEM accumulators of 256 columns.
+// (one 128 B swizzle row). Warps 0-7: epilogue (TMEM lane quarter = warp % 4, column half = warp / 4), warp 8: TMA
+// producer, warp 9: MMA issuer + TMEM allocator, warp 10: per-row coefficients. 4-stage smem ring, 2 TMEM accumulators of 256 columns.
 #include <cuda.h>
 #include <algorithm>
 #include <cmath>
@@ -32,14 +32,16 @@ namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 32, STAGES = 4, UMMA_K = 8;
 constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4, STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int THREADS = 192, EPI_THREADS = 128;
+constexpr int EPI_WARPS = 8, EPI_THREADS = EPI_WARPS * 32, THREADS = EPI_THREADS + 96;   // + TMA, MMA, coefficient warps
+constexpr int W_TMA = EPI_WARPS, W_MMA = EPI_WARPS + 1, W_COEF = EPI_WARPS + 2;
+constexpr int EPI_COLS = BN / (EPI_WARPS / 4);   // columns one epilogue warp scans per tile
 constexpr int R_MAX = 16;              // sampled keys kept per (query, slice)
 constexpr int SAMPLE_STRIDE = 32;      // every 32nd tile is sampled
 constexpr uint32_t TMEM_COLS = 512;
 
 // dynamic shared memory (after rounding the base up to 1024 B)
 struct __align__(16) Ctrl {
-    unsigned long long full[STAGES], empty[STAGES], tfull[2], tempty[2];
+    unsigned long long full[STAGES], empty[STAGES], tfull[2], tempty[2], cfull[2];
     uint32_t tmem_base;
     uint32_t pad[3];
 };
@@ -115,7 +117,7 @@ struct ScanArgs {
     uint32_t first_slot, n, nq, nq_pad, kblocks;
     int metric;
     uint32_t n_tiles, tiles_per_slice;
-    float* samp;                                 // SAMPLE: [slices][nq_pad][R_MAX] ascending
+    float* samp;                                 // SAMPLE: [slices * EPI_WARPS / 4][nq_pad][R_MAX] ascending
     const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
 };
 
@@ -147,10 +149,10 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), 4); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), EPI_WARPS); mbar_init(s32(&ctrl->cfull[i]), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 5) {
+    if (warp == W_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&ctrl->tmem_base)), "r"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -159,7 +161,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     tc_fence_after();
     const uint32_t tmem_base = ctrl->tmem_base;
 
-    if (warp == 4) {
+    if (warp == W_TMA) {
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
@@ -175,7 +177,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                 }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == W_MMA) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0, it = 0;
@@ -202,29 +204,38 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                 umma_commit(s32(&ctrl->tfull[buf]));              // accumulator ready for the epilogue
             }
         }
+    } else if (warp == W_COEF) {
+        // ===== row coefficients (a_j, b_j) of the tile, one buffer per accumulator buffer =====
+        uint32_t it = 0;
+        for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
+            const uint32_t buf = it & 1u;
+            mbar_wait(s32(&ctrl->tempty[buf]), ((it >> 1) & 1u) ^ 1u);      // the epilogue is done with colv[buf]
+            float2 ab[BN / 32];
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) ab[j] = row_coeffs(a, t * BN + j * 32 + lane);
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) colv[buf * BN + j * 32 + lane] = ab[j];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s32(&ctrl->cfull[buf]));
+        }
     } else {
         // ===== epilogue: thread = one query row of the accumulator =====
-        const uint32_t row = threadIdx.x, q = q0 + row;
+        // warp w owns TMEM lanes 32 (w % 4) .. +31 (hardware rule) and the column half w / 4
+        const uint32_t row = (uint32_t)(warp & 3) * 32 + lane, half = (uint32_t)warp >> 2, q = q0 + row;
         const bool qok = q < a.nq;
         float tau = -INFINITY;
         if (EMIT && qok) tau = a.tau[q];
         float top[R_MAX];
 #pragma unroll
         for (int i = 0; i < R_MAX; ++i) top[i] = INFINITY;
-        if (t_first < t_end) {
-            colv[row] = row_coeffs(a, t_first * BN + row);
-            colv[row + EPI_THREADS] = row_coeffs(a, t_first * BN + row + EPI_THREADS);
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
         uint32_t it = 0;
         for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
-            const uint32_t buf = it & 1u, tn = t + t_step;
-            float2 n0 = make_float2(0.f, INFINITY), n1 = n0;
-            if (tn < t_end) { n0 = row_coeffs(a, tn * BN + row); n1 = row_coeffs(a, tn * BN + row + EPI_THREADS); }   // in flight during this tile
+            const uint32_t buf = it & 1u;
+            mbar_wait(s32(&ctrl->cfull[buf]), (it >> 1) & 1u);
             mbar_wait(s32(&ctrl->tfull[buf]), (it >> 1) & 1u);
             tc_fence_after();
-            const float2* cv = colv + buf * BN;
-            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BN;
+            const float2* cv = colv + buf * BN + half * EPI_COLS;
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + buf * BN + half * EPI_COLS;
             // Hot loop: key = a * dot + b and a running minimum, branch-free; the (rare) chunks whose minimum passes
             // the bound are re-scanned element by element. The next 32 columns are in flight while these are processed.
             const float4* cv4 = reinterpret_cast<const float4*>(cv);
@@ -244,7 +255,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                         if (EMIT) {
                             if (key <= tau) {
                                 const uint32_t pos = atomicAdd(&a.cnt[q], 1u);
-                                if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + c * 32 + i;
+                                if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + half * EPI_COLS + c * 32 + i;
                             }
                         } else if (key < top[R_MAX - 1]) {
                             top[R_MAX - 1] = key;
@@ -261,31 +272,28 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
             float va[32], vb[32];
             tmem_ld32_issue(taddr, va);
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; c += 2) {
+            for (int c = 0; c < EPI_COLS / 32; c += 2) {
                 tmem_wait();
                 tmem_ld32_issue(taddr + (c + 1) * 32, vb);
                 process(va, c);
                 tmem_wait();
-                if (c + 2 < BN / 32) tmem_ld32_issue(taddr + (c + 2) * 32, va);
+                if (c + 2 < EPI_COLS / 32) tmem_ld32_issue(taddr + (c + 2) * 32, va);
                 process(vb, c + 1);
             }
 #endif
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s32(&ctrl->tempty[buf]));
-            colv[(buf ^ 1u) * BN + row] = n0;
-            colv[(buf ^ 1u) * BN + row + EPI_THREADS] = n1;
-            asm volatile("bar.sync 1, 128;" ::: "memory");
         }
         if (!EMIT && qok) {
-            float* o = a.samp + ((size_t)slice * a.nq_pad + q) * R_MAX;
+            float* o = a.samp + ((size_t)(slice * (EPI_WARPS / 4) + half) * a.nq_pad + q) * R_MAX;
 #pragma unroll
             for (int i = 0; i < R_MAX; ++i) o[i] = top[i];
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    if (warp == W_MMA) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
 
@@ -486,7 +494,7 @@ bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k)
 size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
     const tc::Plan p = tc::make_plan(nq, n, k, dpad, sm_count);
     using tc::al256;
-    return al256((size_t)nq * 4) * 3 + al256((size_t)p.slices * p.nq_pad * tc::R_MAX * 4) + al256((size_t)nq * p.cap * 4) +
+    return al256((size_t)nq * 4) * 3 + al256((size_t)p.slices * (tc::EPI_WARPS / 4) * p.nq_pad * tc::R_MAX * 4) + al256((size_t)nq * p.cap * 4) +
            al256((size_t)(nq + 2) * 4) + 512;
 }
 
@@ -502,7 +510,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     float* qn = (float*)sp; sp += al256((size_t)q.nq * 4);
     float* tau = (float*)sp; sp += al256((size_t)q.nq * 4);
     uint32_t* cnt = (uint32_t*)sp; sp += al256((size_t)q.nq * 4);
-    float* samp = (float*)sp; sp += al256((size_t)p.slices * p.nq_pad * R_MAX * 4);
+    float* samp = (float*)sp; sp += al256((size_t)p.slices * (EPI_WARPS / 4) * p.nq_pad * R_MAX * 4);
     uint32_t* cand = (uint32_t*)sp; sp += al256((size_t)q.nq * p.cap * 4);
     uint32_t* flag = (uint32_t*)sp;   // [0] n_flagged, [1] max |x|^2 bits, [2..] flagged queries
     CUtensorMap mapQ, mapX;
@@ -520,7 +528,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     a.samp = samp; a.tau = tau; a.cand = cand; a.cnt = cnt; a.cap = p.cap;
     const dim3 grid(p.nqt, p.slices);
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
-    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(samp, p.slices, q.nq, p.nq_pad, p.r, tau);
+    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, tau);
     k_tc_scan<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
     RerankArgs r{};
     r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
