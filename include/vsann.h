@@ -83,7 +83,8 @@ typedef struct vs_stats {
     uint32_t top_level;
     uint32_t reserved32;
     uint64_t exact_tc_queries;   /* exact-mode queries answered by the tensor-core scan + FP32 re-rank */
-    uint64_t exact_tc_fallback;  /* ... of which the FP32 tile kernel had to answer (proof failed)   */
+    uint64_t exact_tc_fallback;  /* ... of which the FP32 tile kernel had to answer (overflow / < k)  */
+    uint64_t exact_tc_second_scan; /* ... of which needed a second tensor scan with a proven threshold */
 } vs_stats;
 
 /* usearch::Index::new + reserve — usearch.rs:82-99 (called from create_index, :38-53). */

@@ -345,76 +345,104 @@ __device__ __forceinline__ float tc_eps(int metric, float qn, float max_xn, uint
 struct RerankArgs {
     const float* vecs; const float* sqn; const uint64_t* slot_key; const uint32_t* deleted;
     uint32_t first_slot, n_slots, dpad;
-    const float* q; size_t q_stride; const float* qn; uint32_t nq;
+    const float* q; size_t q_stride; const float* qn; uint32_t nq;     // the queries of this round (local index)
+    const uint32_t* qmap;                                              // local -> caller's query index (null = identity)
     int metric; uint32_t k, kp, cap;
-    const uint32_t* cand; const uint32_t* cnt; const float* tau; const uint32_t* max_xn_bits;
+    uint32_t* cand; float* cand_d; const uint32_t* cnt; const float* tau; const uint32_t* max_xn_bits;
     uint64_t* out_keys; float* out_dist;
-    uint32_t* n_flagged; uint32_t* flagged;      // queries the FP32 kernel must answer
+    // round 1 only: queries whose proof failed but whose k-th distance is known go to a second scan with
+    // tau2 = key(dk + 2 eps) (a superset of the true top-k by construction)
+    uint32_t* n_r2; uint32_t* r2_ids; float* r2_tau; float* r2_qn;
+    uint32_t* n_fb; uint32_t* fb_ids;                                  // queries only the FP32 kernel can answer
 };
 
-// One warp per query: exact distances of the candidates (sequential fmaf chain over the dimensions,
-// exactly k_exact_tiles / the oracle), top-k by (distance, key), then the proof that no row outside
-// the candidate set can belong to the top-k.
-__global__ void __launch_bounds__(128) k_tc_rerank(RerankArgs a) {
+// Exact distances of the emitted candidates: grid (cap / 128, nq), one warp per 32 candidates. Each lane owns one
+// candidate and runs the oracle's sequential fmaf chain over the dimensions; rows are staged through a
+// transposed shared tile so that the global reads are 128 B coalesced.
+__global__ void __launch_bounds__(128) k_tc_exact_dist(RerankArgs a) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t q = blockIdx.y;
+    const uint32_t cnt = min(a.cnt[q], a.cap);
+    if (blockIdx.x * 128u >= cnt) return;                          // whole block past the end
+    float* qs = reinterpret_cast<float*>(sm);
+    float* tile = qs + a.dpad + (size_t)warp * 32 * 33;
+    for (uint32_t c = threadIdx.x; c < a.dpad; c += blockDim.x) qs[c] = a.q[(size_t)q * a.q_stride + c];
+    __syncthreads();
+    const uint32_t b0 = (blockIdx.x * 4 + warp) * 32;
+    if (b0 >= cnt) return;
+    uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
+    if (slot != NONE && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
+    float acc = 0.f;
+    for (uint32_t kc = 0; kc < a.dpad; kc += 32) {
+        // 32 rows x 32 floats = 256 float4: lane l fetches float4 (it * 32 + l): row = idx / 8, quad = idx % 8
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx = it * 32 + lane, r = idx >> 3, c4 = (idx & 7) * 4;
+            const uint32_t sj = __shfl_sync(0xffffffffu, slot, r);
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sj != NONE && kc + c4 < a.dpad) x = __ldg(reinterpret_cast<const float4*>(a.vecs + (size_t)(sj - a.first_slot) * a.dpad + kc + c4));
+            float* t = tile + r * 33 + c4;
+            t[0] = x.x; t[1] = x.y; t[2] = x.z; t[3] = x.w;
+        }
+        __syncwarp();
+        const uint32_t kend = min(32u, a.dpad - kc);
+        if (a.metric == L2SQ) { for (uint32_t i = 0; i < kend; ++i) { const float d = qs[kc + i] - tile[lane * 33 + i]; acc = fmaf(d, d, acc); } }
+        else { for (uint32_t i = 0; i < kend; ++i) acc = fmaf(qs[kc + i], tile[lane * 33 + i], acc); }
+        __syncwarp();
+    }
+    float d = INFINITY;
+    if (slot != NONE) d = finish_metric(a.metric, acc, a.qn[q], a.metric == COS ? a.sqn[slot - a.first_slot] : 0.f);
+    if (b0 + lane < cnt) { a.cand_d[(size_t)q * a.cap + b0 + lane] = d; a.cand[(size_t)q * a.cap + b0 + lane] = slot; }
+}
+
+// One warp per query: top-k of the candidates by (distance, key), then the proof that no row outside the
+// candidate set can belong to the top-k (rows that were not emitted have key > tau, i.e. exact distance >
+// dist(tau) - eps).
+__global__ void __launch_bounds__(128) k_tc_select(RerankArgs a) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
     const uint32_t q = blockIdx.x * wpb + warp;
     if (q >= a.nq) return;
-    const size_t per_warp = (size_t)a.dpad * 4 + 32 * 33 * 4 + (size_t)a.kp * 16 + 256;
-    unsigned char* base = sm + (size_t)warp * per_warp;
-    float* qs = reinterpret_cast<float*>(base); base += (size_t)a.dpad * 4;
-    float* tile = reinterpret_cast<float*>(base); base += 32 * 33 * 4;
+    unsigned char* base = sm + (size_t)warp * ((size_t)a.kp * 16 + 256);
     SList L;
     L.ld = reinterpret_cast<float*>(base); L.ld2 = L.ld + a.kp; L.li = reinterpret_cast<uint32_t*>(L.ld2 + a.kp); L.li2 = L.li + a.kp;
     uint32_t* scr_id = L.li2 + a.kp; float* scr_d = reinterpret_cast<float*>(scr_id + 32);
     L.cap = (int)a.k; L.capp = (int)a.kp;
     slist_init(L);
-    for (uint32_t c = lane; c < a.dpad; c += 32) qs[c] = a.q[(size_t)q * a.q_stride + c];
-    __syncwarp();
-    const float qn = a.qn[q];
-    const uint32_t total = a.cnt[q];
-    const uint32_t cnt = min(total, a.cap);
+    const uint32_t total = a.cnt[q], cnt = min(total, a.cap);
     const LessByKey less{a.slot_key, a.n_slots};
     for (uint32_t b0 = 0; b0 < cnt; b0 += 32) {
-        uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
-        if (slot != NONE && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
-        float acc = 0.f;
-        for (uint32_t kc = 0; kc < a.dpad; kc += 32) {
-            // coalesced: all lanes read 32 consecutive floats of one candidate row, 32 rows in turn
-#pragma unroll 8
-            for (int j = 0; j < 32; ++j) {
-                const uint32_t sj = __shfl_sync(0xffffffffu, slot, j);
-                float x = 0.f;
-                if (sj != NONE && kc + lane < a.dpad) x = __ldg(a.vecs + (size_t)(sj - a.first_slot) * a.dpad + kc + lane);
-                tile[j * 33 + lane] = x;
-            }
-            __syncwarp();
-            const uint32_t kend = min(32u, a.dpad - kc);
-            if (a.metric == L2SQ) { for (uint32_t i = 0; i < kend; ++i) { const float d = qs[kc + i] - tile[lane * 33 + i]; acc = fmaf(d, d, acc); } }
-            else { for (uint32_t i = 0; i < kend; ++i) acc = fmaf(qs[kc + i], tile[lane * 33 + i], acc); }
-            __syncwarp();
-        }
-        float d = INFINITY;
-        if (slot != NONE) d = finish_metric(a.metric, acc, qn, a.metric == COS ? a.sqn[slot - a.first_slot] : 0.f);
+        const uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
+        const float d = slot != NONE ? a.cand_d[(size_t)q * a.cap + b0 + lane] : INFINITY;
         slist_merge(L, d, slot, scr_id, scr_d, less);
     }
-    // proof: rows that were not emitted have key > tau  =>  exact distance > dist(tau) - eps
-    const float tau = a.tau[q], max_xn = __uint_as_float(*a.max_xn_bits);
+    const float qn = a.qn[q], tau = a.tau[q], max_xn = __uint_as_float(*a.max_xn_bits);
     float tau_dist;
     if (a.metric == L2SQ) tau_dist = qn + tau;
     else if (a.metric == IP) tau_dist = 1.f + tau;
     else tau_dist = qn > 0.f ? 1.f + tau * rsqrtf(qn) : -INFINITY;
+    const float eps = tc_eps(a.metric, qn, max_xn, a.dpad);
     const float dk = L.ld[a.k - 1];
-    const bool full = L.li[a.k - 1] != NONE;
-    const bool proven = total <= a.cap && full && dk < tau_dist - tc_eps(a.metric, qn, max_xn, a.dpad);
-    if (proven) {
+    const bool full = L.li[a.k - 1] != NONE, fits = total <= a.cap;
+    const uint32_t gq = a.qmap ? a.qmap[q] : q;
+    if (fits && full && dk < tau_dist - eps) {
         for (uint32_t i = lane; i < a.k; i += 32) {
-            const uint32_t id = L.li[i];
-            a.out_keys[(size_t)q * a.k + i] = a.slot_key[id];
-            a.out_dist[(size_t)q * a.k + i] = L.ld[i];
+            a.out_keys[(size_t)gq * a.k + i] = a.slot_key[L.li[i]];
+            a.out_dist[(size_t)gq * a.k + i] = L.ld[i];
         }
     } else if (lane == 0) {
-        a.flagged[atomicAdd(a.n_flagged, 1u)] = q;
+        const float t2d = dk + 2.f * eps;
+        float tau2;
+        if (a.metric == L2SQ) tau2 = t2d - qn;
+        else if (a.metric == IP) tau2 = t2d - 1.f;
+        else tau2 = (t2d - 1.f) * sqrtf(qn);
+        if (a.n_r2 && full && qn > 0.f && isfinite(tau2)) {
+            const uint32_t i = atomicAdd(a.n_r2, 1u);
+            a.r2_ids[i] = gq; a.r2_tau[i] = tau2; a.r2_qn[i] = qn;
+        } else {
+            a.fb_ids[atomicAdd(a.n_fb, 1u)] = gq;
+        }
     }
 }
 
@@ -491,74 +519,113 @@ bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k)
     return (uint64_t)c.n * q.nq >= (1ull << 24);
 }
 
+namespace tc {
+struct Scratch {
+    float *qn, *tau, *samp, *cand_d, *r2_tau, *r2_qn, *gq;
+    uint32_t *cnt, *cand, *ctr /* [0] n_r2, [1] max |x|^2 bits, [2] n_fb */, *r2_ids, *fb_ids;
+};
+static size_t carve(const Plan& p, uint32_t nq, uint32_t dpad, unsigned char* base, Scratch* s) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { unsigned char* r = base ? base + off : nullptr; off += al256(bytes); return r; };
+    Scratch t{};
+    t.qn = (float*)take((size_t)nq * 4); t.tau = (float*)take((size_t)nq * 4); t.cnt = (uint32_t*)take((size_t)nq * 4);
+    t.samp = (float*)take((size_t)p.slices * (EPI_WARPS / 4) * p.nq_pad * R_MAX * 4);
+    t.cand = (uint32_t*)take((size_t)nq * p.cap * 4); t.cand_d = (float*)take((size_t)nq * p.cap * 4);
+    t.ctr = (uint32_t*)take(16);
+    t.r2_ids = (uint32_t*)take((size_t)nq * 4); t.r2_tau = (float*)take((size_t)nq * 4); t.r2_qn = (float*)take((size_t)nq * 4);
+    t.fb_ids = (uint32_t*)take((size_t)nq * 4);
+    t.gq = (float*)take((size_t)nq * dpad * 4);
+    if (s) *s = t;
+    return off + 256;
+}
+}  // namespace tc
+
 size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
-    const tc::Plan p = tc::make_plan(nq, n, k, dpad, sm_count);
-    using tc::al256;
-    return al256((size_t)nq * 4) * 3 + al256((size_t)p.slices * (tc::EPI_WARPS / 4) * p.nq_pad * tc::R_MAX * 4) + al256((size_t)nq * p.cap * 4) +
-           al256((size_t)(nq + 2) * 4) + 512;
+    return tc::carve(tc::make_plan(nq, n, k, dpad, sm_count), nq, dpad, nullptr, nullptr);
 }
 
 // Exact top-k of every query; results are those of launch_exact (FP32 kernel) bit for bit.
-// fb_scratch: scratch of the FP32 kernel, sized for nq queries. stats (host, optional): [0] += queries, [1] += queries sent to the FP32 kernel.
+// fb_scratch: scratch of the FP32 kernel, sized for nq queries.
+// stats (host, optional): [0] += queries, [1] += queries answered by the FP32 kernel, [2] += queries that needed the second scan.
 cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint64_t* out_keys, float* out_dist,
                             const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats) {
     using namespace tc;
     if (q.nq == 0) return cudaSuccess;
     const Plan p = make_plan(q.nq, c.n, k, q.dpad, dev.sm_count);
     if (scratch.bytes < exact_tc_scratch_bytes(q.nq, c.n, k, q.dpad, dev.sm_count)) return cudaErrorInvalidValue;
-    unsigned char* sp = (unsigned char*)scratch.ptr;
-    float* qn = (float*)sp; sp += al256((size_t)q.nq * 4);
-    float* tau = (float*)sp; sp += al256((size_t)q.nq * 4);
-    uint32_t* cnt = (uint32_t*)sp; sp += al256((size_t)q.nq * 4);
-    float* samp = (float*)sp; sp += al256((size_t)p.slices * (EPI_WARPS / 4) * p.nq_pad * R_MAX * 4);
-    uint32_t* cand = (uint32_t*)sp; sp += al256((size_t)q.nq * p.cap * 4);
-    uint32_t* flag = (uint32_t*)sp;   // [0] n_flagged, [1] max |x|^2 bits, [2..] flagged queries
+    Scratch S; carve(p, q.nq, q.dpad, (unsigned char*)scratch.ptr, &S);
     CUtensorMap mapQ, mapX;
     if (!make_map(&mapQ, q.q, q.nq, q.dpad, q.stride, BM) || !make_map(&mapX, c.vecs, c.n, q.dpad, c.row_stride, BN)) return cudaErrorNotSupported;
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_tc_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_tc_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(cnt, 0, (size_t)q.nq * 4, st)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(flag, 0, 8, st)) != cudaSuccess) return e;
-    k_query_norms_tc<<<(q.nq + 127) / 128, 128, 0, st>>>(q.q, q.stride, q.dpad, q.nq, qn);
-    k_tc_max_norm<<<dev.sm_count, 256, 0, st>>>(c.sqn, c.n, flag + 1);
+#define TC_TRY(x) do { if ((e = (x)) != cudaSuccess) return e; } while (0)
+    TC_TRY(cudaFuncSetAttribute(k_tc_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    TC_TRY(cudaFuncSetAttribute(k_tc_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    const size_t dsmem = (size_t)q.dpad * 4 + 4 * 32 * 33 * 4, ssmem = 4 * ((size_t)p.kp * 16 + 256);
+    if (dsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+    TC_TRY(cudaFuncSetAttribute(k_tc_exact_dist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
+    TC_TRY(cudaMemsetAsync(S.cnt, 0, (size_t)q.nq * 4, st));
+    TC_TRY(cudaMemsetAsync(S.ctr, 0, 16, st));
+    k_query_norms_tc<<<(q.nq + 127) / 128, 128, 0, st>>>(q.q, q.stride, q.dpad, q.nq, S.qn);
+    k_tc_max_norm<<<dev.sm_count, 256, 0, st>>>(c.sqn, c.n, S.ctr + 1);
+
     ScanArgs a{};
     a.sqn = c.sqn; a.deleted = c.deleted; a.first_slot = c.first_slot; a.n = c.n; a.nq = q.nq; a.nq_pad = p.nq_pad; a.kblocks = p.kblocks;
     a.metric = metric; a.n_tiles = p.n_tiles; a.tiles_per_slice = p.tiles_per_slice;
-    a.samp = samp; a.tau = tau; a.cand = cand; a.cnt = cnt; a.cap = p.cap;
+    a.samp = S.samp; a.tau = S.tau; a.cand = S.cand; a.cnt = S.cnt; a.cap = p.cap;
     const dim3 grid(p.nqt, p.slices);
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
-    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, tau);
+    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, S.tau);
     k_tc_scan<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
+
     RerankArgs r{};
     r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
-    r.q = q.q; r.q_stride = q.stride; r.qn = qn; r.nq = q.nq; r.metric = metric; r.k = k; r.kp = p.kp; r.cap = p.cap;
-    r.cand = cand; r.cnt = cnt; r.tau = tau; r.max_xn_bits = flag + 1; r.out_keys = out_keys; r.out_dist = out_dist;
-    r.n_flagged = flag; r.flagged = flag + 2;
-    const uint32_t wpb = 4; const size_t rsmem = (size_t)wpb * ((size_t)q.dpad * 4 + 32 * 33 * 4 + (size_t)p.kp * 16 + 256);
-    if (rsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
-    if ((e = cudaFuncSetAttribute(k_tc_rerank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem)) != cudaSuccess) return e;
-    k_tc_rerank<<<(q.nq + wpb - 1) / wpb, wpb * 32, rsmem, st>>>(r);
-    if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    uint32_t nf = 0;
-    if ((e = cudaMemcpyAsync(&nf, flag, 4, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
-    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
-    if (stats) { stats[0] += q.nq; stats[1] += nf; }
+    r.q = q.q; r.q_stride = q.stride; r.qn = S.qn; r.nq = q.nq; r.qmap = nullptr; r.metric = metric; r.k = k; r.kp = p.kp; r.cap = p.cap;
+    r.cand = S.cand; r.cand_d = S.cand_d; r.cnt = S.cnt; r.tau = S.tau; r.max_xn_bits = S.ctr + 1; r.out_keys = out_keys; r.out_dist = out_dist;
+    r.n_r2 = S.ctr; r.r2_ids = S.r2_ids; r.r2_tau = S.r2_tau; r.r2_qn = S.r2_qn; r.n_fb = S.ctr + 2; r.fb_ids = S.fb_ids;
+    k_tc_exact_dist<<<dim3((p.cap + 127) / 128, q.nq), 128, dsmem, st>>>(r);
+    k_tc_select<<<(q.nq + 3) / 4, 128, ssmem, st>>>(r);
+    TC_TRY(cudaGetLastError());
+    uint32_t ctr[4] = {0, 0, 0, 0};
+    TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
+    TC_TRY(cudaStreamSynchronize(st));
+    const uint32_t n2 = ctr[0];
+    if (stats) { stats[0] += q.nq; stats[2] += n2; }
+
+    if (n2 > 0) {
+        // second scan for the unproven queries: tau2 = key(dk + 2 eps) emits a superset of the true top-k
+        k_tc_gather_queries<<<std::min<uint32_t>(n2, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.r2_ids, n2, S.gq);
+        const Plan p2 = make_plan(n2, c.n, k, q.dpad, dev.sm_count);
+        CUtensorMap mapQ2;
+        if (!make_map(&mapQ2, S.gq, n2, q.dpad, q.dpad, BM)) return cudaErrorNotSupported;
+        TC_TRY(cudaMemsetAsync(S.cnt, 0, (size_t)n2 * 4, st));
+        ScanArgs a2 = a;
+        a2.nq = n2; a2.nq_pad = p2.nq_pad; a2.n_tiles = p2.n_tiles; a2.tiles_per_slice = p2.tiles_per_slice; a2.tau = S.r2_tau;
+        k_tc_scan<true><<<dim3(p2.nqt, p2.slices), THREADS, SMEM_BYTES, st>>>(mapQ2, mapX, a2);
+        RerankArgs r2 = r;
+        r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = n2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr;
+        k_tc_exact_dist<<<dim3((p.cap + 127) / 128, n2), 128, dsmem, st>>>(r2);
+        k_tc_select<<<(n2 + 3) / 4, 128, ssmem, st>>>(r2);
+        TC_TRY(cudaGetLastError());
+        TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
+        TC_TRY(cudaStreamSynchronize(st));
+    }
+    const uint32_t nf = ctr[2];
+    if (stats) stats[1] += nf;
     if (nf == 0) return cudaSuccess;
-    // unproven queries: FP32 tile kernel on the gathered subset
-    float* gq = nullptr; uint64_t* gk = nullptr; float* gd = nullptr;
-    if ((e = cudaMalloc(&gq, (size_t)nf * q.dpad * 4)) != cudaSuccess) return e;
-    if ((e = cudaMalloc(&gk, (size_t)nf * k * 8)) != cudaSuccess) { cudaFree(gq); return e; }
-    if ((e = cudaMalloc(&gd, (size_t)nf * k * 4)) != cudaSuccess) { cudaFree(gq); cudaFree(gk); return e; }
-    k_tc_gather_queries<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, flag + 2, nf, gq);
-    ExactQueries sub = q; sub.q = gq; sub.stride = q.dpad; sub.nq = nf;
+    // what is left (candidate overflow, fewer than k live candidates): FP32 tile kernel on the gathered subset
+    uint64_t* gk = nullptr; float* gd = nullptr;
+    TC_TRY(cudaMalloc(&gk, (size_t)nf * k * 8));
+    if ((e = cudaMalloc(&gd, (size_t)nf * k * 4)) != cudaSuccess) { cudaFree(gk); return e; }
+    k_tc_gather_queries<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.fb_ids, nf, S.gq);
+    ExactQueries sub = q; sub.q = S.gq; sub.stride = q.dpad; sub.nq = nf;
     e = launch_exact(c, sub, metric, k, k, nullptr, gk, gd, fb_scratch, dev, st);
     if (e == cudaSuccess) {
-        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, k, flag + 2, nf, out_keys, out_dist);
+        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, k, S.fb_ids, nf, out_keys, out_dist);
         e = cudaGetLastError();
     }
-    cudaError_t e2 = cudaStreamSynchronize(st);
-    cudaFree(gq); cudaFree(gk); cudaFree(gd);
+    const cudaError_t e2 = cudaStreamSynchronize(st);
+    cudaFree(gk); cudaFree(gd);
+#undef TC_TRY
     return e != cudaSuccess ? e : e2;
 }
 

@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[2] = {0, 0};
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[3] = {0, 0, 0};
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -491,7 +491,7 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->build_vectors = ix->st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = ix->st_build_batches;
     o->build_seconds = ix->st_build_seconds; o->device_bytes = ix->device_bytes + ix->build_scratch.n + ix->exact_scratch.n;
     o->top_level = (uint32_t)ix->top_level;
-    o->exact_tc_queries = ix->tc_stats[0]; o->exact_tc_fallback = ix->tc_stats[1];
+    o->exact_tc_queries = ix->tc_stats[0]; o->exact_tc_fallback = ix->tc_stats[1]; o->exact_tc_second_scan = ix->tc_stats[2];
     return VS_OK;
 }
 vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; return VS_OK; }
@@ -501,7 +501,7 @@ vs_status vs_reset_stats(vs_index* ix) {
     cudaSetDevice(ix->dev.device);
     CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
-    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->tc_stats[0] = ix->tc_stats[1] = 0;
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->tc_stats[0] = ix->tc_stats[1] = ix->tc_stats[2] = 0;
     return VS_OK;
 }
 
