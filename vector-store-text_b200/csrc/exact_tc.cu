@@ -511,7 +511,8 @@ static inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
 }  // namespace tc
 
 bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k) {
-    static const int mode = [] { const char* e = getenv("VSANN_EXACT_TC"); return e ? atoi(e) : -1; }();   // 0 off, 1 force, default auto
+    const char* env = getenv("VSANN_EXACT_TC");   // 0 = FP32 kernel only, 1 = tensor path whenever it applies, default: by size
+    const int mode = env ? atoi(env) : -1;
     if (mode == 0) return false;
     if (c.row_step != 1 || !c.slot_key || !c.deleted || q.self_step != 0 || k == 0 || k > 128) return false;
     if (q.stride != q.dpad || c.row_stride != q.dpad || c.n < 2 * (uint32_t)tc::BN * tc::SAMPLE_STRIDE) return false;
