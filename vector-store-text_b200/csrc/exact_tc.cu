@@ -349,7 +349,8 @@ struct RerankArgs {
     const uint32_t* qmap;                                              // local -> caller's query index (null = identity)
     int metric; uint32_t k, kp, cap;
     uint32_t* cand; float* cand_d; const uint32_t* cnt; const float* tau; const uint32_t* max_xn_bits;
-    uint64_t* out_keys; float* out_dist;
+    uint64_t* out_keys; uint32_t* out_slots; float* out_dist; uint32_t out_ld;   // out_keys and/or out_slots, rows of out_ld entries
+    uint32_t self_first, self_step;                                    // query g is slot self_first + g * self_step (excluded); 0 = none
     // round 1 only: queries whose proof failed but whose k-th distance is known go to a second scan with
     // tau2 = key(dk + 2 eps) (a superset of the true top-k by construction)
     uint32_t* n_r2; uint32_t* r2_ids; float* r2_tau; float* r2_qn;
@@ -372,7 +373,8 @@ __global__ void __launch_bounds__(128) k_tc_exact_dist(RerankArgs a) {
     const uint32_t b0 = (blockIdx.x * 4 + warp) * 32;
     if (b0 >= cnt) return;
     uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
-    if (slot != NONE && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
+    if (slot != NONE && a.deleted && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
+    if (a.self_step && slot == a.self_first + (a.qmap ? a.qmap[q] : q) * a.self_step) slot = NONE;
     float acc = 0.f;
     for (uint32_t kc = 0; kc < a.dpad; kc += 32) {
         // 32 rows x 32 floats = 256 float4: lane l fetches float4 (it * 32 + l): row = idx / 8, quad = idx % 8
@@ -399,7 +401,8 @@ __global__ void __launch_bounds__(128) k_tc_exact_dist(RerankArgs a) {
 // One warp per query: top-k of the candidates by (distance, key), then the proof that no row outside the
 // candidate set can belong to the top-k (rows that were not emitted have key > tau, i.e. exact distance >
 // dist(tau) - eps).
-__global__ void __launch_bounds__(128) k_tc_select(RerankArgs a) {
+template <class Less>
+__global__ void __launch_bounds__(128) k_tc_select(RerankArgs a, Less less) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
     const uint32_t q = blockIdx.x * wpb + warp;
@@ -411,7 +414,6 @@ __global__ void __launch_bounds__(128) k_tc_select(RerankArgs a) {
     L.cap = (int)a.k; L.capp = (int)a.kp;
     slist_init(L);
     const uint32_t total = a.cnt[q], cnt = min(total, a.cap);
-    const LessByKey less{a.slot_key, a.n_slots};
     for (uint32_t b0 = 0; b0 < cnt; b0 += 32) {
         const uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
         const float d = slot != NONE ? a.cand_d[(size_t)q * a.cap + b0 + lane] : INFINITY;
@@ -427,9 +429,11 @@ __global__ void __launch_bounds__(128) k_tc_select(RerankArgs a) {
     const bool full = L.li[a.k - 1] != NONE, fits = total <= a.cap;
     const uint32_t gq = a.qmap ? a.qmap[q] : q;
     if (fits && full && dk < tau_dist - eps) {
-        for (uint32_t i = lane; i < a.k; i += 32) {
-            a.out_keys[(size_t)gq * a.k + i] = a.slot_key[L.li[i]];
-            a.out_dist[(size_t)gq * a.k + i] = L.ld[i];
+        for (uint32_t i = lane; i < a.out_ld; i += 32) {
+            const uint32_t id = i < a.k ? L.li[i] : NONE;
+            if (a.out_slots) a.out_slots[(size_t)gq * a.out_ld + i] = id;
+            if (a.out_keys) a.out_keys[(size_t)gq * a.out_ld + i] = id == NONE ? 0xFFFFFFFFFFFFFFFFull : a.slot_key[id];
+            if (a.out_dist) a.out_dist[(size_t)gq * a.out_ld + i] = i < a.k ? L.ld[i] : INFINITY;
         }
     } else if (lane == 0) {
         const float t2d = dk + 2.f * eps;
@@ -437,7 +441,8 @@ __global__ void __launch_bounds__(128) k_tc_select(RerankArgs a) {
         if (a.metric == L2SQ) tau2 = t2d - qn;
         else if (a.metric == IP) tau2 = t2d - 1.f;
         else tau2 = (t2d - 1.f) * sqrtf(qn);
-        if (a.n_r2 && full && qn > 0.f && isfinite(tau2)) {
+        // (a truncated candidate set still bounds the k-th distance from above, so overflow is no obstacle here)
+        if (a.n_r2 && full && (a.metric != COS || qn > 0.f) && isfinite(tau2)) {
             const uint32_t i = atomicAdd(a.n_r2, 1u);
             a.r2_ids[i] = gq; a.r2_tau[i] = tau2; a.r2_qn[i] = qn;
         } else {
@@ -452,15 +457,22 @@ __global__ void k_tc_gather_queries(const float* __restrict__ q, size_t q_stride
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
         out[i] = q[(size_t)flagged[i / dpad] * q_stride + (i % dpad)];
 }
-__global__ void k_tc_scatter_results(const uint64_t* __restrict__ keys, const float* __restrict__ dist, uint32_t k, const uint32_t* __restrict__ flagged, uint32_t nf,
+__global__ void k_tc_scatter_results(const uint64_t* __restrict__ keys, const float* __restrict__ dist, uint32_t ld, const uint32_t* __restrict__ flagged, uint32_t nf,
                                      uint64_t* __restrict__ out_keys, float* __restrict__ out_dist) {
-    const size_t total = (size_t)nf * k;
+    const size_t total = (size_t)nf * ld;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t o = (size_t)flagged[i / k] * k + (i % k);
-        out_keys[o] = keys[i]; out_dist[o] = dist[i];
+        const size_t o = (size_t)flagged[i / ld] * ld + (i % ld);
+        if (out_keys) out_keys[o] = keys[i];
+        if (out_dist) out_dist[o] = dist[i];
     }
 }
 
+
+__global__ void k_tc_scatter_slots(const uint32_t* __restrict__ slots, uint32_t ld, const uint32_t* __restrict__ flagged, uint32_t nf, uint32_t* __restrict__ out) {
+    const size_t total = (size_t)nf * ld;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+        out[(size_t)flagged[i / ld] * ld + (i % ld)] = slots[i];
+}
 
 // ---- host side ---------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -514,7 +526,7 @@ bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k)
     const char* env = getenv("VSANN_EXACT_TC");   // 0 = FP32 kernel only, 1 = tensor path whenever it applies, default: by size
     const int mode = env ? atoi(env) : -1;
     if (mode == 0) return false;
-    if (c.row_step != 1 || !c.slot_key || !c.deleted || q.self_step != 0 || k == 0 || k > 128) return false;
+    if (c.row_step != 1 || k == 0 || k > 128) return false;
     if (q.stride != q.dpad || c.row_stride != q.dpad || c.n < 2 * (uint32_t)tc::BN * tc::SAMPLE_STRIDE) return false;
     if (mode == 1) return true;
     return (uint64_t)c.n * q.nq >= (1ull << 24);
@@ -548,12 +560,15 @@ size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad
 // Exact top-k of every query; results are those of launch_exact (FP32 kernel) bit for bit.
 // fb_scratch: scratch of the FP32 kernel, sized for nq queries.
 // stats (host, optional): [0] += queries, [1] += queries answered by the FP32 kernel, [2] += queries that needed the second scan.
-cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint64_t* out_keys, float* out_dist,
+cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
+                            uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
                             const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats) {
     using namespace tc;
     if (q.nq == 0) return cudaSuccess;
-    const Plan p = make_plan(q.nq, c.n, k, q.dpad, dev.sm_count);
-    if (scratch.bytes < exact_tc_scratch_bytes(q.nq, c.n, k, q.dpad, dev.sm_count)) return cudaErrorInvalidValue;
+    if (out_ld < k || (out_keys && !c.slot_key)) return cudaErrorInvalidValue;
+    const uint32_t kplan = k + (q.self_step ? 1u : 0u);     // the query itself is among the candidates and dropped later
+    const Plan p = make_plan(q.nq, c.n, kplan, q.dpad, dev.sm_count);
+    if (scratch.bytes < exact_tc_scratch_bytes(q.nq, c.n, kplan, q.dpad, dev.sm_count)) return cudaErrorInvalidValue;
     Scratch S; carve(p, q.nq, q.dpad, (unsigned char*)scratch.ptr, &S);
     CUtensorMap mapQ, mapX;
     if (!make_map(&mapQ, q.q, q.nq, q.dpad, q.stride, BM) || !make_map(&mapX, c.vecs, c.n, q.dpad, c.row_stride, BN)) return cudaErrorNotSupported;
@@ -581,10 +596,15 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     RerankArgs r{};
     r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
     r.q = q.q; r.q_stride = q.stride; r.qn = S.qn; r.nq = q.nq; r.qmap = nullptr; r.metric = metric; r.k = k; r.kp = p.kp; r.cap = p.cap;
-    r.cand = S.cand; r.cand_d = S.cand_d; r.cnt = S.cnt; r.tau = S.tau; r.max_xn_bits = S.ctr + 1; r.out_keys = out_keys; r.out_dist = out_dist;
+    r.cand = S.cand; r.cand_d = S.cand_d; r.cnt = S.cnt; r.tau = S.tau; r.max_xn_bits = S.ctr + 1; r.out_keys = out_keys; r.out_slots = out_slots; r.out_dist = out_dist; r.out_ld = out_ld;
+    r.self_first = q.self_first; r.self_step = q.self_step;
     r.n_r2 = S.ctr; r.r2_ids = S.r2_ids; r.r2_tau = S.r2_tau; r.r2_qn = S.r2_qn; r.n_fb = S.ctr + 2; r.fb_ids = S.fb_ids;
     k_tc_exact_dist<<<dim3((p.cap + 127) / 128, q.nq), 128, dsmem, st>>>(r);
-    k_tc_select<<<(q.nq + 3) / 4, 128, ssmem, st>>>(r);
+    auto select = [&](const RerankArgs& ra, uint32_t nqs) {
+        if (c.slot_key) k_tc_select<LessByKey><<<(nqs + 3) / 4, 128, ssmem, st>>>(ra, LessByKey{c.slot_key, c.n_slots});
+        else k_tc_select<LessById><<<(nqs + 3) / 4, 128, ssmem, st>>>(ra, LessById());
+    };
+    select(r, q.nq);
     TC_TRY(cudaGetLastError());
     uint32_t ctr[4] = {0, 0, 0, 0};
     TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
@@ -595,7 +615,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     if (n2 > 0) {
         // second scan for the unproven queries: tau2 = key(dk + 2 eps) emits a superset of the true top-k
         k_tc_gather_queries<<<std::min<uint32_t>(n2, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.r2_ids, n2, S.gq);
-        const Plan p2 = make_plan(n2, c.n, k, q.dpad, dev.sm_count);
+        const Plan p2 = make_plan(n2, c.n, kplan, q.dpad, dev.sm_count);
         CUtensorMap mapQ2;
         if (!make_map(&mapQ2, S.gq, n2, q.dpad, q.dpad, BM)) return cudaErrorNotSupported;
         TC_TRY(cudaMemsetAsync(S.cnt, 0, (size_t)n2 * 4, st));
@@ -605,7 +625,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
         RerankArgs r2 = r;
         r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = n2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr;
         k_tc_exact_dist<<<dim3((p.cap + 127) / 128, n2), 128, dsmem, st>>>(r2);
-        k_tc_select<<<(n2 + 3) / 4, 128, ssmem, st>>>(r2);
+        select(r2, n2);
         TC_TRY(cudaGetLastError());
         TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
         TC_TRY(cudaStreamSynchronize(st));
@@ -613,19 +633,25 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     const uint32_t nf = ctr[2];
     if (stats) stats[1] += nf;
     if (nf == 0) return cudaSuccess;
-    // what is left (candidate overflow, fewer than k live candidates): FP32 tile kernel on the gathered subset
-    uint64_t* gk = nullptr; float* gd = nullptr;
-    TC_TRY(cudaMalloc(&gk, (size_t)nf * k * 8));
-    if ((e = cudaMalloc(&gd, (size_t)nf * k * 4)) != cudaSuccess) { cudaFree(gk); return e; }
+    // what is left (fewer than k live candidates, overflow twice): FP32 tile kernel
+    if (q.self_step) {   // self-exclusion is positional: redo the whole block (insertion batches; rare)
+        e = launch_exact(c, q, metric, k, out_ld, out_slots, out_keys, out_dist, fb_scratch, dev, st);
+        return e != cudaSuccess ? e : cudaStreamSynchronize(st);
+    }
+    uint64_t* gk = nullptr; float* gd = nullptr; uint32_t* gs = nullptr;
+    TC_TRY(cudaMalloc(&gk, (size_t)nf * out_ld * 8));
+    if ((e = cudaMalloc(&gd, (size_t)nf * out_ld * 4)) != cudaSuccess) { cudaFree(gk); return e; }
+    if (out_slots && (e = cudaMalloc(&gs, (size_t)nf * out_ld * 4)) != cudaSuccess) { cudaFree(gk); cudaFree(gd); return e; }
     k_tc_gather_queries<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.fb_ids, nf, S.gq);
     ExactQueries sub = q; sub.q = S.gq; sub.stride = q.dpad; sub.nq = nf;
-    e = launch_exact(c, sub, metric, k, k, nullptr, gk, gd, fb_scratch, dev, st);
+    e = launch_exact(c, sub, metric, k, out_ld, gs, out_keys ? gk : nullptr, gd, fb_scratch, dev, st);
     if (e == cudaSuccess) {
-        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, k, S.fb_ids, nf, out_keys, out_dist);
+        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, out_ld, S.fb_ids, nf, out_keys, out_dist);
+        if (out_slots) k_tc_scatter_slots<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gs, out_ld, S.fb_ids, nf, out_slots);
         e = cudaGetLastError();
     }
     const cudaError_t e2 = cudaStreamSynchronize(st);
-    cudaFree(gk); cudaFree(gd);
+    cudaFree(gk); cudaFree(gd); cudaFree(gs);
 #undef TC_TRY
     return e != cudaSuccess ? e : e2;
 }

@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[3] = {0, 0, 0};
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[3] = {0, 0, 0}, tc_build_stats[3] = {0, 0, 0};
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -214,6 +214,12 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         ExactQueries q{}; q.q = c.vecs; q.stride = c.row_stride; q.nq = b.items[l]; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = fs; q.self_step = s;
         const uint32_t k = std::min<uint32_t>(KNN_BATCH, b.items[l] - 1);
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
+        if (exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
+            CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count)));
+            ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
+            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, ix->tc_build_stats));
+            continue;
+        }
         CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ix->stream));
     }
     CU(cudaMemsetAsync(ix->lt.n_edges, 0, 8, ix->stream));
@@ -297,7 +303,7 @@ vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t
             // tcgen05 TF32 scan + exact FP32 re-rank (exact_tc.cu); same ids and distance bits as the FP32 kernel
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes((uint32_t)nq, c.n, (uint32_t)k, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
-            CU(launch_exact_tc(c, q, ix->metric, (uint32_t)k, d_keys, d_dist, ts, sc, ix->dev, st, ix->tc_stats));
+            CU(launch_exact_tc(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, ts, sc, ix->dev, st, ix->tc_stats));
             return VS_OK;
         }
         CU(launch_exact(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, sc, ix->dev, st));

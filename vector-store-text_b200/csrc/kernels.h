@@ -89,7 +89,8 @@ cudaError_t launch_exact(const ExactCorpus& c, const ExactQueries& q, int metric
 // Tensor-core (tcgen05 TF32 + exact FP32 re-rank) form of launch_exact for contiguous corpora; same results.
 bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k);
 size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count);
-cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint64_t* out_keys, float* out_dist,
+cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
+                            uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
                             const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats);
 
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
