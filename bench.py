@@ -135,6 +135,23 @@ def cpu_leg(vst, args, x, q, ef, steps, warmup):
     return out
 
 
+def cpu_pick_ef(vst, args, x, q):
+    cores = int(os.environ.get("SCYLLA_USEARCH_BACKGROUND_THREADS", "0")) or (os.cpu_count() or 1)
+    n = min(args.cpu_sample, x.shape[0], 50_000)
+    o = vst.VsIndex(D, metric=vst.Metric.L2SQ, connectivity=M, expansion_add=EF_ADD, capacity_hint=n, lib=load_oracle(vst))
+    o.set_threads(cores)
+    o.add_batch(np.arange(n, dtype=np.uint64), x[:n])
+    truth, _, _ = o.search(q[:200], K_NN, exact=True)
+    pick = EF_PARITY
+    for ef in (16, 24, 32, 48, 64):
+        ak, _, _ = o.search(q[:200], K_NN, ef=ef)
+        if recall(ak, truth) >= 0.95:
+            pick = ef
+            break
+    o.close()
+    return pick
+
+
 def algorithmic_counts(vst, g, x, q, ef, sample=200):
     """Work of the sequential algorithm (oracle beam, oracle/oracle_vsann.cpp ovs_graph_search) on the
     GPU-built graph for a query sample: distance evaluations and expansions per query."""
@@ -183,7 +200,9 @@ def run_reference(args):
     import vector_store_text_b200 as vst
     x = gen(min(args.n, args.cpu_sample), D, 42, args.dist)
     q = gen(args.nq, D, 43, args.dist)
-    ef = args.ef or EF_PARITY
+    ef = args.ef
+    if not ef:   # the smallest ef that reaches recall@10 >= 0.95 on the reference arm's own graph
+        ef = cpu_pick_ef(vst, args, x, q)
     cb = cpu_leg(vst, args, x, q, ef, args.steps, args.warmup)
     line = {"impl": "reference", "metric": "ann_qps_at_recall95", "value": cb["value"], "unit": "queries/s", "n_gpus": args.gpus,
             "steps": cb["steps"], "warmup": min(args.warmup, 1), "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
@@ -192,6 +211,10 @@ def run_reference(args):
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def shard_q_fn(world, nq):
+    return world * nq
 
 
 def workload_name(args):
@@ -319,6 +342,12 @@ def main():
     # the search kernel alone (no collective) for the roofline
     ms_kernel = timed(lambda: g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=chosen, stream=stream), args.steps, 1)
 
+    # ---- brute-force mode (K1 on tcgen05 + exact re-rank): the same 10k x 1M batch, timed like a step -----
+    g.set_stats(True); g.reset_stats()
+    ms_exact = timed(lambda: search_step(0, exact=True), max(2, args.steps // 2), 1)
+    st_exact = g.stats()
+    g.set_stats(False)
+
     # ---- e2e: same batch through the C ABI with pinned HOST buffers (H2D + D2H inside) --------------
     qh = torch.from_numpy(q).pin_memory()
     kh = torch.empty((nq, K_NN), dtype=torch.int64).pin_memory()
@@ -359,6 +388,23 @@ def main():
         alg_bytes = (ev * D * 4 + ex * row_bytes) * nq
         achieved = alg_bytes / (ms_kernel * 1e-3) / 1e9
         cb = None if args.no_cpu else cpu_leg(vst, args, x, q, chosen, 3, 1)
+        traffic = None
+        try:   # DRAM bytes per launch of the search kernel from the committed ncu --set full capture (profiles/)
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_k_search_traffic.json")))["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        scans = max(1, st_exact["exact_tc_scans"])
+        scan_ms = 1e3 * st_exact["exact_tc_scan_seconds"] / scans
+        tf32_peak = peaks.get("bf16_tflops", 1590.0) / 2.0
+        exact_tf = 2.0 * nq * n * D / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None
+        exact = {"mode": "brute force, bit-identical ids and distances (tcgen05 TF32 scan + exact FP32 re-rank + proof)",
+                 "qps": shard_q_fn(world, nq) / (ms_exact * 1e-3), "ms_per_batch": ms_exact,
+                 "tc_queries": st_exact["exact_tc_queries"], "second_scan_queries": st_exact["exact_tc_second_scan"],
+                 "fp32_fallback_queries": st_exact["exact_tc_fallback"],
+                 "roofline": {"bound": "tensor", "kernel": "k_tc_scan<EMIT>", "achieved": exact_tf, "peak": tf32_peak, "unit": "TFLOP/s",
+                              "frac": (exact_tf / tf32_peak) if exact_tf else None, "kernel_ms": scan_ms,
+                              "peak_source": "TF32 = half the measured bf16 burst rate (MEASURED_PEAKS.json bf16_tflops / 2)",
+                              "flops_per_launch": 2.0 * nq * n * D}}
         shard_q = world * nq
         line = {
             "metric": "ann_qps_at_recall95", "value": shard_q / (ms * 1e-3), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
@@ -376,8 +422,9 @@ def main():
             "e2e": {"value": shard_q / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * D * 4, "d2h_bytes_per_step": nq * K_NN * 12,
                     "ms_per_step": e2e_ms, "recall_at_10": e2e_recall},
             "gpu_launches": args.steps,
-            "roofline": {"bound": "hbm", "kernel": "k_search", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": None, "peak_source": peak_src, "kernel_ms": ms_kernel,
+            "exact": exact,
+            "roofline": {"bound": "hbm", "kernel": "k_search_t", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": traffic, "peak_source": peak_src, "kernel_ms": ms_kernel,
                          "algorithmic": {"dist_evals_per_query": ev, "expansions_per_query": ex, "bytes_per_query": ev * D * 4 + ex * row_bytes,
                                          "source": "oracle beam (ovs_graph_search) on the GPU-built graph, 200-query sample"}},
             "cpu_baseline": cb, "clocks": clocks,

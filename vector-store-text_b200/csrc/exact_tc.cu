@@ -559,10 +559,9 @@ size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad
 
 // Exact top-k of every query; results are those of launch_exact (FP32 kernel) bit for bit.
 // fb_scratch: scratch of the FP32 kernel, sized for nq queries.
-// stats (host, optional): [0] += queries, [1] += queries answered by the FP32 kernel, [2] += queries that needed the second scan.
 cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
                             uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
-                            const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats) {
+                            const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, TcStats* stats) {
     using namespace tc;
     if (q.nq == 0) return cudaSuccess;
     if (out_ld < k || (out_keys && !c.slot_key)) return cudaErrorInvalidValue;
@@ -591,7 +590,11 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     const dim3 grid(p.nqt, p.slices);
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
     k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, S.tau);
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    const bool timing = stats && stats->time_scan && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess;
+    if (timing) cudaEventRecord(ev0, st);
     k_tc_scan<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
+    if (timing) cudaEventRecord(ev1, st);
 
     RerankArgs r{};
     r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
@@ -610,7 +613,10 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
     TC_TRY(cudaStreamSynchronize(st));
     const uint32_t n2 = ctr[0];
-    if (stats) { stats[0] += q.nq; stats[2] += n2; }
+    if (stats) { stats->queries += q.nq; stats->second_scan += n2; stats->scans++; }
+    if (timing) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) stats->scan_ms += ms; }
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
 
     if (n2 > 0) {
         // second scan for the unproven queries: tau2 = key(dk + 2 eps) emits a superset of the true top-k
@@ -631,7 +637,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
         TC_TRY(cudaStreamSynchronize(st));
     }
     const uint32_t nf = ctr[2];
-    if (stats) stats[1] += nf;
+    if (stats) stats->fp32_fallback += nf;
     if (nf == 0) return cudaSuccess;
     // what is left (fewer than k live candidates, overflow twice): FP32 tile kernel
     if (q.self_step) {   // self-exclusion is positional: redo the whole block (insertion batches; rare)

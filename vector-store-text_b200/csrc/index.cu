@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; uint64_t tc_stats[3] = {0, 0, 0}, tc_build_stats[3] = {0, 0, 0};
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats;
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -217,7 +217,7 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         if (exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
-            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, ix->tc_build_stats));
+            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, &ix->tc_build_stats));
             continue;
         }
         CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ix->stream));
@@ -303,7 +303,7 @@ vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t
             // tcgen05 TF32 scan + exact FP32 re-rank (exact_tc.cu); same ids and distance bits as the FP32 kernel
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes((uint32_t)nq, c.n, (uint32_t)k, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
-            CU(launch_exact_tc(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, ts, sc, ix->dev, st, ix->tc_stats));
+            CU(launch_exact_tc(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, ts, sc, ix->dev, st, &ix->tc_stats));
             return VS_OK;
         }
         CU(launch_exact(c, q, ix->metric, (uint32_t)k, (uint32_t)k, nullptr, d_keys, d_dist, sc, ix->dev, st));
@@ -497,17 +497,18 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->build_vectors = ix->st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = ix->st_build_batches;
     o->build_seconds = ix->st_build_seconds; o->device_bytes = ix->device_bytes + ix->build_scratch.n + ix->exact_scratch.n;
     o->top_level = (uint32_t)ix->top_level;
-    o->exact_tc_queries = ix->tc_stats[0]; o->exact_tc_fallback = ix->tc_stats[1]; o->exact_tc_second_scan = ix->tc_stats[2];
+    o->exact_tc_queries = ix->tc_stats.queries; o->exact_tc_fallback = ix->tc_stats.fp32_fallback; o->exact_tc_second_scan = ix->tc_stats.second_scan;
+    o->exact_tc_scans = ix->tc_stats.scans; o->exact_tc_scan_seconds = ix->tc_stats.scan_ms * 1e-3;
     return VS_OK;
 }
-vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; return VS_OK; }
+vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; ix->tc_stats.time_scan = on != 0; return VS_OK; }
 vs_status vs_reset_stats(vs_index* ix) {
     if (!ix) return VS_ERR_INVALID;
     std::lock_guard<std::mutex> g(ix->mu);
     cudaSetDevice(ix->dev.device);
     CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
-    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->tc_stats[0] = ix->tc_stats[1] = ix->tc_stats[2] = 0;
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; { const bool t = ix->tc_stats.time_scan; ix->tc_stats = TcStats(); ix->tc_stats.time_scan = t; }
     return VS_OK;
 }
 

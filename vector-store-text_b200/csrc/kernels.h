@@ -86,12 +86,17 @@ cudaError_t launch_exact(const ExactCorpus& c, const ExactQueries& q, int metric
                          uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
                          const ExactScratch& scratch, const DeviceInfo& dev, cudaStream_t st);
 
+struct TcStats {                    // host-side counters of the tensor-core exact path
+    uint64_t queries = 0, fp32_fallback = 0, second_scan = 0, scans = 0;
+    double scan_ms = 0;             // device time of the full (emit) scans, measured with events when time_scan is set
+    bool time_scan = false;
+};
 // Tensor-core (tcgen05 TF32 + exact FP32 re-rank) form of launch_exact for contiguous corpora; same results.
 bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k);
 size_t exact_tc_scratch_bytes(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count);
 cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int metric, uint32_t k, uint32_t out_ld,
                             uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
-                            const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, uint64_t* stats);
+                            const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, TcStats* stats);
 
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                           uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st);
