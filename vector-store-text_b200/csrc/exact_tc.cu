@@ -36,7 +36,7 @@ constexpr int EPI_WARPS = 8, EPI_THREADS = EPI_WARPS * 32, THREADS = EPI_THREADS
 constexpr int W_TMA = EPI_WARPS, W_MMA = EPI_WARPS + 1, W_COEF = EPI_WARPS + 2;
 constexpr int EPI_COLS = BN / (EPI_WARPS / 4);   // columns one epilogue warp scans per tile
 constexpr int R_MAX = 16;              // sampled keys kept per (query, slice)
-constexpr int SAMPLE_STRIDE = 32;      // every 32nd tile is sampled
+constexpr int SAMPLE_STRIDE = 32;      // large corpora: every 32nd tile is sampled (small ones: Plan::stride)
 constexpr uint32_t TMEM_COLS = 512;
 
 // dynamic shared memory (after rounding the base up to 1024 B)
@@ -116,7 +116,7 @@ struct ScanArgs {
     const float* sqn; const uint32_t* deleted;   // sqn by row, tombstones by slot (row r is slot first_slot + r)
     uint32_t first_slot, n, nq, nq_pad, kblocks;
     int metric;
-    uint32_t n_tiles, tiles_per_slice;
+    uint32_t n_tiles, tiles_per_slice, sample_stride;
     float* samp;                                 // SAMPLE: [slices * EPI_WARPS / 4][nq_pad][R_MAX] ascending
     const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
 };
@@ -144,8 +144,8 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t q0 = blockIdx.x * BM, slice = blockIdx.y;
     const uint32_t t_begin = slice * a.tiles_per_slice, t_end = min(a.n_tiles, t_begin + a.tiles_per_slice);
-    const uint32_t t_step = EMIT ? 1u : (uint32_t)SAMPLE_STRIDE;
-    const uint32_t t_first = EMIT ? t_begin : ((t_begin + SAMPLE_STRIDE - 1) / SAMPLE_STRIDE) * SAMPLE_STRIDE;
+    const uint32_t t_step = EMIT ? 1u : a.sample_stride;
+    const uint32_t t_first = EMIT ? t_begin : ((t_begin + a.sample_stride - 1) / a.sample_stride) * a.sample_stride;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), 1); }
@@ -498,7 +498,13 @@ static bool make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t 
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, kblocks, r, cap, kp; };
+struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, kblocks, stride, r, cap, kp; bool ok; };
+
+// r-th smallest of a 1/stride sample as threshold: expected stride * r rows pass, P(fewer than k pass) < 1e-3
+static uint32_t sample_rank(uint32_t k, uint32_t stride) {
+    const float lam = (float)k / stride;
+    return (uint32_t)std::ceil(lam + 4.f * std::sqrt(lam) + 3.5f);
+}
 
 static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
     Plan p;
@@ -508,11 +514,15 @@ static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm
     uint32_t want = (8u * (uint32_t)sm_count + p.nqt - 1) / p.nqt;          // ~8 waves of CTAs
     want = std::min<uint32_t>(want, std::max<uint32_t>(1u, p.n_tiles / 8));   // >= 8 tiles per CTA
     want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 64u));
-    p.tiles_per_slice = (p.n_tiles + want - 1) / want;
+    p.tiles_per_slice = std::max<uint32_t>(1u, (p.n_tiles + want - 1) / want);
     p.slices = (p.n_tiles + p.tiles_per_slice - 1) / p.tiles_per_slice;
-    const float lam = (float)k / SAMPLE_STRIDE;
-    p.r = std::min<uint32_t>(R_MAX, (uint32_t)std::ceil(lam + 4.f * std::sqrt(lam) + 3.5f));
-    uint32_t cap = 1; while (cap < 4u * p.r * SAMPLE_STRIDE) cap <<= 1;
+    // sampling stride: 32 on large corpora (the sample pass is the slow one per tile), denser on small ones so
+    // that fewer rows pass the threshold; never so dense that the rank exceeds the R_MAX keys a thread keeps
+    uint32_t smin = 1; while (smin < SAMPLE_STRIDE && sample_rank(k, smin) > R_MAX) ++smin;
+    p.stride = p.n_tiles >= 512 ? SAMPLE_STRIDE : std::min<uint32_t>(SAMPLE_STRIDE, std::max<uint32_t>(smin, p.n_tiles / 16));
+    p.ok = sample_rank(k, p.stride) <= R_MAX && p.n_tiles >= 2 * p.stride;
+    p.r = std::min<uint32_t>(R_MAX, sample_rank(k, p.stride));
+    uint32_t cap = 1; while (cap < 4u * p.r * p.stride) cap <<= 1;
     p.cap = cap;
     p.kp = (k + 31u) & ~31u;
     return p;
@@ -526,8 +536,9 @@ bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k)
     const char* env = getenv("VSANN_EXACT_TC");   // 0 = FP32 kernel only, 1 = tensor path whenever it applies, default: by size
     const int mode = env ? atoi(env) : -1;
     if (mode == 0) return false;
-    if (c.row_step != 1 || k == 0 || k > 128) return false;
-    if (q.stride != q.dpad || c.row_stride != q.dpad || c.n < 2 * (uint32_t)tc::BN * tc::SAMPLE_STRIDE) return false;
+    if (c.row_step != 1 || k == 0 || k > 128 || c.n == 0 || q.nq == 0) return false;
+    if (q.stride != q.dpad || c.row_stride != q.dpad) return false;
+    if (!tc::make_plan(q.nq, c.n, k + (q.self_step ? 1u : 0u), q.dpad, 148).ok) return false;
     if (mode == 1) return true;
     return (uint64_t)c.n * q.nq >= (1ull << 24);
 }
@@ -585,7 +596,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
 
     ScanArgs a{};
     a.sqn = c.sqn; a.deleted = c.deleted; a.first_slot = c.first_slot; a.n = c.n; a.nq = q.nq; a.nq_pad = p.nq_pad; a.kblocks = p.kblocks;
-    a.metric = metric; a.n_tiles = p.n_tiles; a.tiles_per_slice = p.tiles_per_slice;
+    a.metric = metric; a.n_tiles = p.n_tiles; a.tiles_per_slice = p.tiles_per_slice; a.sample_stride = p.stride;
     a.samp = S.samp; a.tau = S.tau; a.cand = S.cand; a.cnt = S.cnt; a.cap = p.cap;
     const dim3 grid(p.nqt, p.slices);
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);

@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats;
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats; bool build_tc = true;
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -214,7 +214,7 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         ExactQueries q{}; q.q = c.vecs; q.stride = c.row_stride; q.nq = b.items[l]; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = fs; q.self_step = s;
         const uint32_t k = std::min<uint32_t>(KNN_BATCH, b.items[l] - 1);
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
-        if (exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
+        if (ix->build_tc && exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
             CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, &ix->tc_build_stats));
@@ -351,6 +351,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_HASH_FACTOR")) { const long v = atol(e); if (v > 0) ix->dev.hash_factor = (uint32_t)v; }
     if (const char* e = getenv("VSANN_SMEM_LIST")) ix->dev.force_smem_list = atoi(e) != 0;
     if (const char* e = getenv("VSANN_STAGE_BYTES")) ix->dev.stage_bytes = (uint32_t)atol(e);
+    if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
     vs_status s = VS_OK;
     auto body = [&]() -> vs_status {
         CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
