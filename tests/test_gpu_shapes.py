@@ -45,3 +45,32 @@ def test_config_shape(vst, oracle_lib, name, n, d, metric, k, nq, efs):
         assert np.all(np.diff(ad, axis=1) >= 0)
         assert np.all(ak != np.uint64(0xFFFFFFFFFFFFFFFF))
     g.close()
+
+
+def test_c1_via_the_native_index_actor(vst):
+    """BASELINE configs[0]: 10k x 128-d cosine, add + 1k ANN queries k=10 *via the index actor* — here the C++ actor
+    (csrc/actor.cpp: channel 10, 2 x T in flight, bimap) over the GPU library, one message per vector / query."""
+    import time
+    n, d, nq, k = 10000, 128, 1000, 10
+    x = make_data(n, d, 71, clustered=True, centres=256); q = make_data(nq, d, 72, clustered=True, centres=256)
+    a = vst.NativeActor("vector.ann", d, metric=vst.Metric.COS, capacity_hint=n, threads=8)
+    for i in range(n):
+        a.add_or_replace(("pk", i), x[i])
+    t0 = time.time()
+    while a.count() != n and time.time() - t0 < 60:
+        time.sleep(0.01)
+    assert a.count() == n
+    truth_ix = vst.VsIndex(d, metric=vst.Metric.COS, capacity_hint=n, connectivity=2, expansion_add=8)
+    truth_ix.add_batch(np.arange(n, dtype=np.uint64), x)
+    truth, _, _ = truth_ix.search(q, k, exact=True)
+    hits = 0
+    for i in range(nq):
+        pks, dist = a.ann(q[i], k)
+        assert len(pks) == k and all(dist[j] <= dist[j + 1] for j in range(k - 1))
+        hits += len({p[1] for p in pks} & set(truth[i].tolist()))
+    rec = hits / (nq * k)
+    print(f"c1 via native actor: recall@10 = {rec:.4f}")
+    assert rec >= 0.80
+    st = a.stats()
+    assert st["keys"] == n and st["max_queued"] <= 10 and st["max_in_flight"] <= 16
+    a.close(); truth_ix.close()

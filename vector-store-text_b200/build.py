@@ -13,6 +13,23 @@ FLAGS = os.environ.get("VSANN_NVCC_FLAGS", "").split() + ["-gencode", "arch=comp
          "-Xcompiler", "-fPIC,-O2,-Wall", "--threads", "4"]
 
 
+ACTOR_OUT = os.path.join(HERE, "lib", "libvsactor.so")
+ACTOR_SRC = os.path.join(CSRC, "actor.cpp")
+ACTOR_DEPS = [ACTOR_SRC, os.path.join(HERE, "..", "include", "vsactor.h"), os.path.join(HERE, "..", "include", "vsann.h")]
+
+
+def build_actor(force: bool = False) -> str:
+    """libvsactor.so: the index-actor shim (host C++ only, no CUDA) over any include/vsann.h backend."""
+    if not force and os.path.exists(ACTOR_OUT) and all(os.path.getmtime(d) <= os.path.getmtime(ACTOR_OUT) for d in ACTOR_DEPS):
+        return ACTOR_OUT
+    os.makedirs(os.path.dirname(ACTOR_OUT), exist_ok=True)
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-fPIC", "-Wall", "-Wextra", "-pthread", "-shared", "-o", ACTOR_OUT, ACTOR_SRC]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return ACTOR_OUT
+
+
 def needs_build() -> bool:
     if not os.path.exists(OUT):
         return True
@@ -22,6 +39,7 @@ def needs_build() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    build_actor(force)
     if not force and not needs_build():
         return OUT
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
