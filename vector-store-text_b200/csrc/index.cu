@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats; bool build_tc = true;
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats; bool build_tc = true, zero_copy = true;
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -351,6 +351,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_HASH_FACTOR")) { const long v = atol(e); if (v > 0) ix->dev.hash_factor = (uint32_t)v; }
     if (const char* e = getenv("VSANN_SMEM_LIST")) ix->dev.force_smem_list = atoi(e) != 0;
     if (const char* e = getenv("VSANN_STAGE_BYTES")) ix->dev.stage_bytes = (uint32_t)atol(e);
+    if (const char* e = getenv("VSANN_ZERO_COPY")) ix->zero_copy = atoi(e) != 0;   // 0: always stage host queries with a copy
     if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
     vs_status s = VS_OK;
     auto body = [&]() -> vs_status {
@@ -454,10 +455,25 @@ vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, si
     std::lock_guard<std::mutex> g(ix->mu);
     vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
     cudaSetDevice(ix->dev.device);
-    CU(ix->qdense.ensure(nq * ix->dims)); CU(ix->out_k.ensure(nq * k)); CU(ix->out_d.ensure(nq * k));
+    CU(ix->out_k.ensure(nq * k)); CU(ix->out_d.ensure(nq * k));
     s = wait_user(ix, ix->stream); if (s != VS_OK) return s;
-    CU(cudaMemcpyAsync(ix->qdense.p, qs, nq * ix->dims * 4, cudaMemcpyHostToDevice, ix->stream));
-    s = search_device_locked(ix, nq, ix->qdense.p, k, ef, exact, ix->out_k.p, ix->out_d.p, ix->stream); if (s != VS_OK) return s;
+    // Pinned (page-locked, UVA-mapped) query buffers are read by the traversal kernel in place: every warp
+    // fetches its 4 d bytes over PCIe while the others compute, so the H2D copy leaves the critical path.
+    // Pageable buffers, and the exact path (which streams the queries many times through TMA), are staged.
+    const float* d_q = nullptr;
+    if (!exact && ix->zero_copy) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, qs) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) d_q = (const float*)at.devicePointer;
+        else cudaGetLastError();
+    }
+    if (!d_q) {
+        CU(ix->qdense.ensure(nq * ix->dims));
+        CU(cudaMemcpyAsync(ix->qdense.p, qs, nq * ix->dims * 4, cudaMemcpyHostToDevice, ix->stream));
+        d_q = ix->qdense.p;
+    }
+    s = search_device_locked(ix, nq, d_q, k, ef, exact, ix->out_k.p, ix->out_d.p, ix->stream); if (s != VS_OK) return s;
+    // (results: writing them straight into pinned host memory from the kernel was measured and is no faster than
+    // this 12 k B per query copy, so the explicit copy stays)
     CU(cudaMemcpyAsync(keys_out, ix->out_k.p, nq * k * 8, cudaMemcpyDeviceToHost, ix->stream));
     CU(cudaMemcpyAsync(dist_out, ix->out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
