@@ -26,6 +26,7 @@
 #include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
+#include "tmap.h"
 
 namespace vsann {
 namespace tc {
@@ -475,27 +476,9 @@ __global__ void k_tc_scatter_slots(const uint32_t* __restrict__ slots, uint32_t 
 }
 
 // ---- host side ---------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = [] {
-        void* p = nullptr; cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) p = nullptr;
-        return (EncodeTiledFn)p;
-    }();
-    return fn;
-}
 // rows x dpad f32 matrix, row-major; box = box_rows x 32 floats, 128 B swizzle, zero fill outside
 static bool make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t dpad, size_t row_stride_floats, uint32_t box_rows) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return false;
-    const cuuint64_t dims[2] = {dpad, rows};
-    const cuuint64_t strides[1] = {(cuuint64_t)row_stride_floats * 4};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
-    const cuuint32_t estr[2] = {1, 1};
-    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return make_tmap_f32(m, base, rows, dpad, row_stride_floats, BK, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, kblocks, stride, r, cap, kp; bool ok; };

@@ -6,8 +6,10 @@
 // restatement in oracle/oracle_vsann.cpp (hnsw_search / hnsw_insert / select_heuristic).
 #include <algorithm>
 #include <atomic>
+#include <cstring>
 #include "tbeam.cuh"
 #include "kernels.h"
+#include "tmap.h"
 
 #ifndef VSANN_T_MINB
 #define VSANN_T_MINB 6   // resident blocks per SM the staged kernels are compiled for
@@ -122,7 +124,7 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
 // Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
 // float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+__global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                      uint32_t ef, uint32_t hsize, uint32_t stage_rows,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                      unsigned long long* counters, uint32_t* work) {
@@ -131,6 +133,7 @@ __global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(GraphView g, con
     const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
     WarpSmem S; WarpStage T;
     carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
+    if (use_vmap) T.tmap = &vmap;
     uint32_t evals = 0, exps = 0, done = 0;
     for (;;) {   // persistent warps: every warp draws its next query from a device counter (no tail, no intra-block wait)
         uint32_t q = 0;
@@ -258,13 +261,14 @@ __global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBat
 
 // Bulk-copy staged variant of K4a (tbeam.cuh).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, VSANN_T_MINB) k_build_search_t(GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize, uint32_t stage_rows,
+__global__ void __launch_bounds__(128, VSANN_T_MINB) k_build_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, BuildBatch b, uint32_t ef, uint32_t efp, uint32_t hsize, uint32_t stage_rows,
                                                            unsigned long long* counters, uint32_t* work) {
     extern __shared__ __align__(128) unsigned char smem[];
     const unsigned warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
     WarpSmem S; WarpStage T;
     carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
+    if (use_vmap) T.tmap = &vmap;
     uint32_t evals = 0, exps = 0;
     for (;;) {
         uint32_t it = 0;
@@ -519,10 +523,16 @@ static cudaError_t next_work_counter(const DeviceInfo& dev, cudaStream_t st, uin
 // ---- staged (bulk-copy) launch geometry: per-warp staging budget -> rows per round ----
 static inline uint32_t stage_rows_for(const GraphView& g, const DeviceInfo& dev) {
     const uint32_t row_bytes = g.dpad * 4;
-    uint32_t rows = dev.stage_bytes / row_bytes;
+    uint32_t rows = (dev.stage_bytes / row_bytes) & ~3u;     // whole gather4 groups
     if (rows > 32) rows = 32;
-    if (rows < 2) rows = 2;
+    if (rows < 4) rows = 4;
     return rows;
+}
+// vecs as a [slots][dpad] tensor with a one-row box for tile::gather4 (rows of at most 256 elements)
+static inline int vecs_tmap(const GraphView& g, const DeviceInfo& dev, CUtensorMap* m) {
+    memset(m, 0, sizeof(*m));
+    if (!dev.gather4 || g.dpad > 256 || (g.dpad & 7u) || g.n_slots == 0) return 0;   // groups of 4 rows must stay 128 B aligned
+    return make_tmap_f32(m, g.vecs, g.n_slots, g.dpad, g.dpad, g.dpad, 1, CU_TENSOR_MAP_SWIZZLE_NONE) ? 1 : 0;
 }
 static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev) {
     uint32_t hs = next_pow2(ef * dev.hash_factor);
@@ -542,7 +552,8 @@ static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, u
     uint32_t* work = nullptr;
     if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
     const uint32_t blocks = std::min<uint32_t>((nq + wpb - 1) / wpb, (uint32_t)dev.sm_count * VSANN_T_MINB);
-    k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work);
+    CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
+    k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work);
     return cudaGetLastError();
 }
 template <int NL>
@@ -564,7 +575,8 @@ static cudaError_t launch_build_search_t(const GraphView& g, const BuildBatch& b
     uint32_t* work = nullptr;
     if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
     const uint32_t blocks = std::min<uint32_t>((b.count + wpb - 1) / wpb, (uint32_t)dev.sm_count * VSANN_T_MINB);
-    k_build_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(g, b, ef, build_efp(ef), hs, rows, counters, work);
+    CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
+    k_build_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(vmap, use_vmap, g, b, ef, build_efp(ef), hs, rows, counters, work);
     return cudaGetLastError();
 }
 template <int NL>

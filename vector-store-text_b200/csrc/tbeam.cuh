@@ -9,6 +9,7 @@
 // as it is accepted. Distances use the accumulation order of warp_dist32 (8-lane teams, chunk
 // c = tl + 8 i, xor-4/2/1 reduction), so both paths return identical bits.
 #pragma once
+#include <cuda.h>
 #include "rbeam.cuh"
 
 namespace vsann {
@@ -39,6 +40,11 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// four rows of a 2-D tensor (arbitrary row indices, box = one row) -> four consecutive rows in shared memory
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap* map, uint32_t bar, int r0, int r1, int r2, int r3) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(0), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) {
 #ifndef VSANN_NO_PREFETCH
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
@@ -54,8 +60,9 @@ struct WarpStage {
     uint32_t buf_s;             // its shared-space address
     uint32_t bar;               // shared-space address of the warp's mbarrier
     uint32_t parity;            // parity of the next completion
-    uint32_t rows;              // staging capacity in rows
+    uint32_t rows;              // staging capacity in rows (a multiple of 4)
     uint32_t row_bytes;         // dpad * 4
+    const CUtensorMap* tmap;    // vecs as a [slots][dpad] tensor with a one-row box (null: rows longer than a TMA box)
 };
 
 // per-warp layout: query | scr_id[32] | scr_d[32] | mbarrier (16 B) | visited hash | staging rows (128 B aligned)
@@ -75,7 +82,7 @@ __device__ __forceinline__ void carve_tsmem(unsigned char* base, uint32_t dpad, 
     S.hmask = hsize - 1;
     p = base + ((((size_t)(p - base)) + 127) & ~(size_t)127);
     T.buf = p; T.buf_s = smem_u32(p);
-    T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0;
+    T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0; T.tmap = nullptr;
     S.L.ld = S.L.ld2 = nullptr; S.L.li = S.L.li2 = nullptr; S.L.cap = S.L.capp = 0;
     if (lane_id() == 0) mbar_init(T.bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -121,7 +128,20 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
     for (int base = 0; base < nvalid; base += (int)T.rows) {
         const int n = min((int)T.rows, nvalid - base);
         float vn = 0.f;
-        if (T.row_bytes > BULK_MIN_ROW_BYTES) {
+        if (T.tmap) {
+            // TMA gather4: one instruction fetches four scattered rows (the issue loop is serialised per
+            // instruction, so a quarter of the instructions is a quarter of the issue cost)
+            const int ngroups = (n + 3) >> 2;
+            if (lane == 0) mbar_arrive_expect_tx(T.bar, (uint32_t)ngroups * 4u * T.row_bytes);
+            if ((int)lane < ngroups) {
+                const int j = 4 * (int)lane;
+                const uint32_t r0 = S.scr_id[base + j];
+                const uint32_t r1 = j + 1 < n ? S.scr_id[base + j + 1] : r0, r2 = j + 2 < n ? S.scr_id[base + j + 2] : r0, r3 = j + 3 < n ? S.scr_id[base + j + 3] : r0;
+                tma_gather4(T.buf_s + (uint32_t)j * T.row_bytes, T.tmap, T.bar, (int)r0, (int)r1, (int)r2, (int)r3);
+            }
+            if (METRIC == COS && (int)lane < n) vn = g.sqn[S.scr_id[base + lane]];
+            mbar_wait(T.bar, T.parity); T.parity ^= 1u;
+        } else if (T.row_bytes > BULK_MIN_ROW_BYTES) {
             // long rows: one bulk copy (UBLKCP) per row, completion on the warp's mbarrier
             if (lane == 0) mbar_arrive_expect_tx(T.bar, (uint32_t)n * T.row_bytes);
             if ((int)lane < n) {
