@@ -55,6 +55,16 @@ struct RList {
         refresh_worst();
     }
 
+    // First unexpanded entry, not marked: the node the next pop() returns unless something closer is inserted first.
+    __device__ __forceinline__ uint32_t peek() const {
+#pragma unroll
+        for (int j = 0; j < NL; ++j) {
+            const unsigned m = __ballot_sync(0xffffffffu, id[j] != NONE && !(id[j] & EXPANDED));
+            if (m) return __shfl_sync(0xffffffffu, id[j], __ffs(m) - 1);
+        }
+        return NONE;
+    }
+
     // First unexpanded entry; marks it expanded. NONE when the beam is finished.
     __device__ __forceinline__ uint32_t pop(float& d_out) {
         const unsigned lane = lane_id();

@@ -58,16 +58,16 @@ constexpr uint32_t BULK_MIN_ROW_BYTES = 0;
 struct WarpStage {
     const unsigned char* buf;   // rows x row_bytes staging area (generic pointer)
     uint32_t buf_s;             // its shared-space address
-    uint32_t bar;               // shared-space address of the warp's mbarrier
-    uint32_t parity;            // parity of the next completion
+    uint32_t bar;               // shared-space address of the warp's mbarriers (slot s: bar + 8 s)
+    uint32_t parity;            // bit s: parity of slot s's next completion
     uint32_t rows;              // staging capacity in rows (a multiple of 4)
     uint32_t row_bytes;         // dpad * 4
     const CUtensorMap* tmap;    // vecs as a [slots][dpad] tensor with a one-row box (null: rows longer than a TMA box)
 };
 
-// per-warp layout: query | scr_id[32] | scr_d[32] | mbarrier (16 B) | visited hash | staging rows (128 B aligned)
+// per-warp layout: query | scr_id[32] | scr_d[32] | 8 mbarriers (one per staging slot of four rows) | visited hash | staging rows (128 B aligned)
 __host__ __device__ inline size_t tsmem_bytes(uint32_t dpad, uint32_t hsize, uint32_t rows) {
-    size_t b = (size_t)dpad * 4 + 256 + 16 + (size_t)hsize * 4;
+    size_t b = (size_t)dpad * 4 + 256 + 64 + (size_t)hsize * 4;
     b = (b + 127) & ~(size_t)127;
     return b + (size_t)rows * dpad * 4;
 }
@@ -77,14 +77,14 @@ __device__ __forceinline__ void carve_tsmem(unsigned char* base, uint32_t dpad, 
     S.q4 = reinterpret_cast<float4*>(p); p += (size_t)dpad * 4;
     S.scr_id = reinterpret_cast<uint32_t*>(p); p += 128;
     S.scr_d = reinterpret_cast<float*>(p); p += 128;
-    T.bar = smem_u32(p); p += 16;
+    T.bar = smem_u32(p); p += 64;
     S.hs = reinterpret_cast<uint32_t*>(p); p += (size_t)hsize * 4;
     S.hmask = hsize - 1;
     p = base + ((((size_t)(p - base)) + 127) & ~(size_t)127);
     T.buf = p; T.buf_s = smem_u32(p);
     T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0; T.tmap = nullptr;
     S.L.ld = S.L.ld2 = nullptr; S.L.li = S.L.li2 = nullptr; S.L.cap = S.L.capp = 0;
-    if (lane_id() == 0) mbar_init(T.bar, 1);
+    if (lane_id() < 8) mbar_init(T.bar + 8u * lane_id(), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncwarp();
 }
@@ -112,7 +112,26 @@ __device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, floa
     }
 }
 
+// One group = four rows into staging slot `slot` (4 x row_bytes), completion on that slot's mbarrier. Called by ONE lane.
+// With a tensor map it is a single TMA gather4 (four scattered rows per instruction), else four bulk copies.
+__device__ __forceinline__ void stage_issue_group(const GraphView& g, const WarpSmem& S, const WarpStage& T, int grp, int slot) {
+    const uint4 r = *reinterpret_cast<const uint4*>(S.scr_id + 4 * grp);
+    const uint32_t bar = T.bar + 8u * (uint32_t)slot, dst = T.buf_s + (uint32_t)slot * 4u * T.row_bytes;
+    mbar_arrive_expect_tx(bar, 4u * T.row_bytes);
+    if (T.tmap) {
+        tma_gather4(dst, T.tmap, bar, (int)r.x, (int)r.y, (int)r.z, (int)r.w);
+    } else {
+        bulk_g2s(dst, g.vecs + (size_t)r.x * g.dpad, T.row_bytes, bar);
+        bulk_g2s(dst + T.row_bytes, g.vecs + (size_t)r.y * g.dpad, T.row_bytes, bar);
+        bulk_g2s(dst + 2u * T.row_bytes, g.vecs + (size_t)r.z * g.dpad, T.row_bytes, bar);
+        bulk_g2s(dst + 3u * T.row_bytes, g.vecs + (size_t)r.w * g.dpad, T.row_bytes, bar);
+    }
+}
+
 // Distances from the warp's query to up to 32 rows, one id per lane (NONE = skip); +inf for skipped lanes.
+// The rows stream through the staging area in groups of four (one per 8-lane team), rows/4 groups in flight:
+// while a group's distances are computed the next groups are still landing, and a freed slot is refilled at once,
+// so an expansion with more rows than the staging area holds pays the memory latency once, not once per refill.
 template <int METRIC, int CPL>
 __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
                                                 uint32_t id, uint32_t& n_evals) {
@@ -121,86 +140,37 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
     if (valid == 0u) return INFINITY;
     const int nvalid = __popc(valid);
     const int pos = __popc(valid & ((1u << lane) - 1u));
+    const uint32_t first = __shfl_sync(0xffffffffu, id, __ffs(valid) - 1);
     if (id != NONE) S.scr_id[pos] = id;
+    if ((int)lane >= nvalid) S.scr_id[lane] = first;   // pad the last group with a row that is fetched anyway
     __syncwarp();
     n_evals += nvalid;
     const int chunks = g.chunks;
-    for (int base = 0; base < nvalid; base += (int)T.rows) {
-        const int n = min((int)T.rows, nvalid - base);
-        float vn = 0.f;
-        if (T.tmap) {
-            // TMA gather4: one instruction fetches four scattered rows (the issue loop is serialised per
-            // instruction, so a quarter of the instructions is a quarter of the issue cost)
-            const int ngroups = (n + 3) >> 2;
-            if (lane == 0) mbar_arrive_expect_tx(T.bar, (uint32_t)ngroups * 4u * T.row_bytes);
-            if ((int)lane < ngroups) {
-                const int j = 4 * (int)lane;
-                const uint32_t r0 = S.scr_id[base + j];
-                const uint32_t r1 = j + 1 < n ? S.scr_id[base + j + 1] : r0, r2 = j + 2 < n ? S.scr_id[base + j + 2] : r0, r3 = j + 3 < n ? S.scr_id[base + j + 3] : r0;
-                tma_gather4(T.buf_s + (uint32_t)j * T.row_bytes, T.tmap, T.bar, (int)r0, (int)r1, (int)r2, (int)r3);
-            }
-            if (METRIC == COS && (int)lane < n) vn = g.sqn[S.scr_id[base + lane]];
-            mbar_wait(T.bar, T.parity); T.parity ^= 1u;
-        } else if (T.row_bytes > BULK_MIN_ROW_BYTES) {
-            // long rows: one bulk copy (UBLKCP) per row, completion on the warp's mbarrier
-            if (lane == 0) mbar_arrive_expect_tx(T.bar, (uint32_t)n * T.row_bytes);
-            if ((int)lane < n) {
-                const uint32_t rid = S.scr_id[base + lane];
-                bulk_g2s(T.buf_s + lane * T.row_bytes, g.vecs + (size_t)rid * g.dpad, T.row_bytes, T.bar);
-                if (METRIC == COS) vn = g.sqn[rid];
-            }
-            mbar_wait(T.bar, T.parity); T.parity ^= 1u;
+    const int ngroups = (nvalid + 3) >> 2, ns = (int)(T.rows >> 2);
+    if ((int)lane < min(ns, ngroups)) stage_issue_group(g, S, T, (int)lane, (int)lane);
+    if (METRIC == COS) { if (id != NONE) S.scr_d[pos] = g.sqn[id]; __syncwarp(); }
+    int slot = 0;
+    for (int grp = 0; grp < ngroups; ++grp) {
+        mbar_wait(T.bar + 8u * (uint32_t)slot, (T.parity >> slot) & 1u); T.parity ^= 1u << slot;
+        const int j = 4 * grp + (int)team;
+        const float4* x4 = reinterpret_cast<const float4*>(T.buf + ((size_t)slot * 4u + team) * T.row_bytes);
+        float acc = 0.f;
+        if (CPL > 0) {
+            float4 x[CPL > 0 ? CPL : 1];
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) x[i] = x4[tl + 8 * i];
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) acc_chunk<METRIC>(Q.v[i], x[i], acc);
         } else {
-            // short rows: 16 B per lane and request (LDGSTS); a 512 B row is one warp-wide request
-            if (CPL > 0 && CPL * 8 == 32) {
 #pragma unroll 4
-                for (int j = 0; j < n; ++j) {
-                    const uint32_t rid = S.scr_id[base + j];
-                    cp_async16(T.buf_s + j * T.row_bytes + lane * 16u, g.vecs + (size_t)rid * g.dpad + lane * 4u);
-                }
-            } else {
-                for (int j = 0; j < n; ++j) {
-                    const uint32_t rid = S.scr_id[base + j];
-                    for (int c = lane; c < chunks; c += 32)
-                        cp_async16(T.buf_s + j * T.row_bytes + c * 16u, g.vecs + (size_t)rid * g.dpad + c * 4u);
-                }
-            }
-            cp_async_commit();
-            if (METRIC == COS && (int)lane < n) vn = g.sqn[S.scr_id[base + lane]];
-            cp_async_wait_all();
-            __syncwarp();
+            for (int c = tl; c < chunks; c += 8) acc_chunk<METRIC>(S.q4[c], x4[c], acc);
         }
-        if (METRIC == COS) { if ((int)lane < n) S.scr_d[base + lane] = vn; __syncwarp(); }
-        for (int jb = 0; jb < n; jb += 8) {   // warp-uniform trip count: the shuffles below need every lane
-            const int j0 = jb + (int)team, j1 = j0 + 4;
-            const bool one = j0 < n, two = j1 < n;
-            const float4* xa = reinterpret_cast<const float4*>(T.buf + (size_t)(one ? j0 : 0) * T.row_bytes);
-            const float4* xb = reinterpret_cast<const float4*>(T.buf + (size_t)(two ? j1 : 0) * T.row_bytes);
-            float acc_a = 0.f, acc_b = 0.f;
-            if (CPL > 0) {
 #pragma unroll
-                for (int i = 0; i < CPL; ++i) {
-                    const float4 x = xa[tl + 8 * i], y = xb[tl + 8 * i];
-                    acc_chunk<METRIC>(Q.v[i], x, acc_a); acc_chunk<METRIC>(Q.v[i], y, acc_b);
-                }
-            } else {
-#pragma unroll 4
-                for (int c = tl; c < chunks; c += 8) {
-                    const float4 x = xa[c], y = xb[c], q = S.q4[c];
-                    acc_chunk<METRIC>(q, x, acc_a); acc_chunk<METRIC>(q, y, acc_b);
-                }
-            }
-#pragma unroll
-            for (int o = 4; o >= 1; o >>= 1) {
-                acc_a += __shfl_xor_sync(0xffffffffu, acc_a, o);
-                acc_b += __shfl_xor_sync(0xffffffffu, acc_b, o);
-            }
-            if (tl == 0) {
-                if (one) S.scr_d[base + j0] = finish_metric(METRIC, acc_a, qn, METRIC == COS ? S.scr_d[base + j0] : 0.f);
-                if (two) S.scr_d[base + j1] = finish_metric(METRIC, acc_b, qn, METRIC == COS ? S.scr_d[base + j1] : 0.f);
-            }
-        }
-        __syncwarp();   // staging rows are free again, distances visible
+        for (int o = 4; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (tl == 0 && j < nvalid) S.scr_d[j] = finish_metric(METRIC, acc, qn, METRIC == COS ? S.scr_d[j] : 0.f);
+        __syncwarp();   // the slot's rows are consumed, distances visible
+        if (grp + ns < ngroups && lane == 0) stage_issue_group(g, S, T, grp + ns, slot);
+        if (++slot == ns) slot = 0;
     }
     const float d = id != NONE ? S.scr_d[pos] : INFINITY;
     __syncwarp();
@@ -257,13 +227,21 @@ template <int NL, int CPL>
 __device__ __forceinline__ void tbeam_level(const GraphView& g, int level, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q,
                                             RList<NL>& L, float qn, uint32_t& evals, uint32_t& exps) {
     const unsigned lane = lane_id();
+    // The link row of the most likely NEXT node is loaded while the current one is expanded (a row is at most
+    // 32 links: one per lane, one register): when the guess holds, a beam step has one dependent memory round
+    // trip (the vector gather) instead of two.
+    uint32_t spec_id = NONE, spec_nb = NONE;
     for (;;) {
         float dc; const uint32_t c = L.pop(dc);
         if (c == NONE) break;
         ++exps;
         int width; const uint32_t* row = level_row(g, level, c, width);
-        for (int off = 0; off < width; off += 32) {
-            uint32_t nb = (off + (int)lane < width) ? row[off + lane] : NONE;
+        uint32_t nb_row = spec_nb;
+        if (c != spec_id) nb_row = ((int)lane < width) ? row[lane] : NONE;
+        spec_id = L.peek();
+        if (spec_id != NONE) { int w2; const uint32_t* r2 = level_row(g, level, spec_id, w2); spec_nb = ((int)lane < w2) ? r2[lane] : NONE; }
+        {
+            uint32_t nb = nb_row;
             if (nb != NONE && nb >= g.n_slots) nb = NONE;
             if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
             __syncwarp();
