@@ -306,8 +306,8 @@ def main():
         sweep[ef] = round(r, 4)
         if r >= 0.95 and chosen is None:
             chosen = ef
-            if ef >= EF_PARITY:
-                break
+        if chosen is not None and ef >= EF_PARITY:
+            break
     if EF_PARITY not in sweep:
         sweep[EF_PARITY] = round(recall(search_step(EF_PARITY).cpu().numpy().view(np.uint64), truth), 4)
     reached = chosen is not None

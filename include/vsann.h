@@ -81,7 +81,7 @@ typedef struct vs_stats {
     double   build_seconds;      /* device time spent inside insertion batches              */
     uint64_t device_bytes;       /* HBM held by this index                                  */
     uint32_t top_level;
-    uint32_t reserved32;
+    uint32_t dims;                /* embedding dimensions (what a loaded index was saved with) */
     uint64_t exact_tc_queries;   /* exact-mode queries answered by the tensor-core scan + FP32 re-rank */
     uint64_t exact_tc_fallback;  /* ... of which the FP32 tile kernel had to answer (overflow / < k)  */
     uint64_t exact_tc_second_scan; /* ... of which needed a second tensor scan with a proven threshold */
@@ -147,6 +147,23 @@ vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k,
  * Query the sizes first with links_out == NULL. */
 vs_status vs_export_level(vs_index* index, uint32_t level, uint32_t* links_out,
                           size_t* n_rows, size_t* row_width, uint64_t* slot_keys_out, size_t* slots);
+
+/* ---- persistence -------------------------------------------------------------
+ * The reference has none: the index is RAM-only and is rebuilt from a full table scan whenever it
+ * is (re)created (src/db_index.rs:108-117,217-237; no usearch save/load/view call anywhere). These
+ * two calls dump and restore the landed state - vectors, norms, every link table, slot keys and
+ * tombstones - so that a restart costs one file read instead of a rebuild. The restored index
+ * answers every query with the same ids and distances as the saved one and accepts further
+ * add / remove calls.
+ *
+ * vs_index_save flushes staged adds first. File: 128-byte header ("VSANNIDX", format version,
+ * dims, metric, connectivity, expansions, slot count, live count), the arrays in a fixed order,
+ * and a 64-bit checksum of everything before it. */
+vs_status vs_index_save(vs_index* index, const char* path);
+/* `overrides` may be NULL; only device, capacity_hint and max_batch are read from it (the index
+ * geometry comes from the file). Errors: VS_ERR_INVALID (unreadable / not an index file /
+ * truncated / checksum mismatch), VS_ERR_UNSUPPORTED (newer format), VS_ERR_CUDA, VS_ERR_CAPACITY. */
+vs_status vs_index_load(const char* path, const vs_options* overrides, vs_index** out);
 
 /* Thread-local message of the last failing call on this thread. */
 const char* vs_last_error(void);

@@ -366,7 +366,7 @@ vs_status ovs_get_stats(vs_index* ix, vs_stats* o) {
     std::memset(o, 0, sizeof(*o));
     o->count = ix->live; o->slots = ix->n_slots; o->capacity = ix->capacity;
     o->search_queries = ix->c_sq; o->search_dist_evals = ix->c_sde; o->search_expansions = ix->c_sx;
-    o->build_vectors = ix->c_bv; o->build_dist_evals = ix->c_bde; o->top_level = ix->max_level < 0 ? 0 : ix->max_level;
+    o->build_vectors = ix->c_bv; o->build_dist_evals = ix->c_bde; o->top_level = ix->max_level < 0 ? 0 : ix->max_level; o->dims = (uint32_t)ix->dims;
     return VS_OK;
 }
 vs_status ovs_set_stats(vs_index*, int) { return VS_OK; }

@@ -9,6 +9,8 @@ from ._ffi import (Metric, VsError, VsIndex, lib_path, load_library, merge_topk_
                    VS_ERR_NOMEM, VS_ERR_UNSUPPORTED, ABI_SYMBOLS)
 from .index import IndexActor, IndexFactory, AnnError  # noqa: F401
 from .actor_native import NativeActor, load_actor_library, actor_lib_path, ACTOR_SYMBOLS  # noqa: F401
+from .service import DbEmbedding, ItemsMonitor, Engine, HttpServer  # noqa: F401
 
 __all__ = ["Metric", "VsError", "VsIndex", "IndexActor", "IndexFactory", "AnnError", "lib_path",
-           "load_library", "merge_topk_device", "NativeActor", "load_actor_library"]
+           "load_library", "merge_topk_device", "NativeActor", "load_actor_library", "DbEmbedding", "ItemsMonitor",
+           "Engine", "HttpServer"]

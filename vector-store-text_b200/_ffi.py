@@ -12,7 +12,7 @@ ABI_SYMBOLS = [
     "vs_index_create", "vs_index_destroy", "vs_add", "vs_add_batch", "vs_add_batch_device", "vs_remove",
     "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_count", "vs_capacity", "vs_reserve",
     "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_export_level",
-    "vs_last_error", "vs_version",
+    "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
 ]
 
 
@@ -33,11 +33,11 @@ class VsStats(C.Structure):
                 ("search_queries", C.c_uint64), ("search_dist_evals", C.c_uint64), ("search_expansions", C.c_uint64),
                 ("build_vectors", C.c_uint64), ("build_dist_evals", C.c_uint64), ("build_batches", C.c_uint64),
                 ("build_seconds", C.c_double), ("device_bytes", C.c_uint64), ("top_level", C.c_uint32),
-                ("reserved32", C.c_uint32), ("exact_tc_queries", C.c_uint64), ("exact_tc_fallback", C.c_uint64),
+                ("dims", C.c_uint32), ("exact_tc_queries", C.c_uint64), ("exact_tc_fallback", C.c_uint64),
                 ("exact_tc_second_scan", C.c_uint64), ("exact_tc_scans", C.c_uint64), ("exact_tc_scan_seconds", C.c_double)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved32"}
+        return {k: getattr(self, k) for k, _ in self._fields_}
 
 
 class VsError(RuntimeError):
@@ -93,6 +93,8 @@ def load_library(path: str = None, prefix: str = "vs_"):
             "search_batch_device": (C.c_int, [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_int, vp, vp, vp]),
             "merge_topk_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "export_level": (C.c_int, [vp, C.c_uint32, vp, szp, szp, vp, szp]),
+            "index_save": (C.c_int, [vp, C.c_char_p]),
+            "index_load": (C.c_int, [C.c_char_p, C.POINTER(VsOptions), C.POINTER(vp)]),
         })
     else:
         sig.update({
@@ -146,6 +148,26 @@ class VsIndex:
         if self._h is not None:
             self._fn("index_destroy")(self._h)
             self._h = None
+
+    # -- persistence (include/vsann.h: vs_index_save / vs_index_load; absent in the reference) ----
+    def save(self, path):
+        self._check(self._fn("index_save")(self._h, os.fsencode(path)))
+
+    @classmethod
+    def load(cls, path, device=0, capacity_hint=0, max_batch=0, lib=None):
+        self = cls.__new__(cls)
+        self.lib = lib or load_library()
+        self.p = self.lib._vs_prefix
+        self._h = None
+        opt = VsOptions(dims=0, metric=0, connectivity=0, expansion_add=0, expansion_search=0,
+                        capacity_hint=capacity_hint, device=device, max_batch=max_batch)
+        h = C.c_void_p()
+        self._check(self._fn("index_load")(os.fsencode(path), C.byref(opt), C.byref(h)))
+        self._h = h
+        st = VsStats()
+        self._check(self._fn("get_stats")(self._h, C.byref(st)))
+        self.dims = int(st.dims)
+        return self
 
     def __del__(self):
         try:

@@ -514,7 +514,7 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->search_queries = c[0]; o->search_dist_evals = c[1]; o->search_expansions = c[2];
     o->build_vectors = ix->st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = ix->st_build_batches;
     o->build_seconds = ix->st_build_seconds; o->device_bytes = ix->device_bytes + ix->build_scratch.n + ix->exact_scratch.n;
-    o->top_level = (uint32_t)ix->top_level;
+    o->top_level = (uint32_t)ix->top_level; o->dims = ix->dims;
     o->exact_tc_queries = ix->tc_stats.queries; o->exact_tc_fallback = ix->tc_stats.fp32_fallback; o->exact_tc_second_scan = ix->tc_stats.second_scan;
     o->exact_tc_scans = ix->tc_stats.scans; o->exact_tc_scan_seconds = ix->tc_stats.scan_ms * 1e-3;
     return VS_OK;
@@ -550,6 +550,139 @@ vs_status vs_export_level(vs_index* ix, uint32_t level, uint32_t* links_out, siz
     if (links_out && nr) CU(cudaMemcpy(links_out, level == 0 ? ix->links0 : ix->linksU[level], nr * w * 4, cudaMemcpyDeviceToHost));
     if (slot_keys_out && ix->n_slots) CU(cudaMemcpy(slot_keys_out, ix->slot_key, (size_t)ix->n_slots * 8, cudaMemcpyDeviceToHost));
     return VS_OK;
+}
+
+// ---- persistence (vsann.h; the reference rebuilds from a table scan instead, db_index.rs:108-117,217-237) ----
+namespace {
+struct FileHeader {          // 128 bytes, little endian
+    char magic[8];           // "VSANNIDX"
+    uint32_t version, dims, dpad, metric, M, efA, efS, n_levels_used;
+    uint64_t n_slots, live;
+    uint32_t max_batch, reserved32;
+    uint64_t reserved[8];
+};
+static_assert(sizeof(FileHeader) == 128, "header layout");
+constexpr uint32_t FILE_VERSION = 1;
+
+struct Summer {              // order-dependent 64-bit checksum over 8-byte words (tail bytes zero-padded)
+    uint64_t h = 0x9E3779B97F4A7C15ull;
+    void add(const void* p, size_t n) {
+        const unsigned char* b = (const unsigned char*)p;
+        size_t i = 0;
+        for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h = (h ^ w) * 0x100000001B3ull; h ^= h >> 29; }
+        if (i < n) { uint64_t w = 0; std::memcpy(&w, b + i, n - i); h = (h ^ w) * 0x100000001B3ull; h ^= h >> 29; }
+    }
+};
+
+// device array <-> file through a bounded host buffer
+vs_status dump(FILE* f, Summer& sum, const void* dptr, size_t bytes, std::vector<unsigned char>& buf) {
+    for (size_t off = 0; off < bytes; off += buf.size()) {
+        const size_t n = std::min(buf.size(), bytes - off);
+        CU(cudaMemcpy(buf.data(), (const unsigned char*)dptr + off, n, cudaMemcpyDeviceToHost));
+        sum.add(buf.data(), n);
+        if (fwrite(buf.data(), 1, n, f) != n) return fail(VS_ERR_INVALID, "save: short write");
+    }
+    return VS_OK;
+}
+vs_status restore(FILE* f, Summer& sum, void* dptr, size_t bytes, std::vector<unsigned char>& buf) {
+    for (size_t off = 0; off < bytes; off += buf.size()) {
+        const size_t n = std::min(buf.size(), bytes - off);
+        if (fread(buf.data(), 1, n, f) != n) return fail(VS_ERR_INVALID, "load: file is truncated");
+        sum.add(buf.data(), n);
+        CU(cudaMemcpy((unsigned char*)dptr + off, buf.data(), n, cudaMemcpyHostToDevice));
+    }
+    return VS_OK;
+}
+struct FileCloser { FILE* f; ~FileCloser() { if (f) fclose(f); } };
+}  // namespace
+
+vs_status vs_index_save(vs_index* ix, const char* path) {
+    if (!ix || !path) return fail(VS_ERR_INVALID, "save: null argument");
+    std::lock_guard<std::mutex> g(ix->mu);
+    vs_status s = flush_locked(ix, nullptr, 0, nullptr); if (s != VS_OK) return s;
+    cudaSetDevice(ix->dev.device);
+    CU(cudaStreamSynchronize(ix->stream));
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(VS_ERR_INVALID, std::string("save: cannot open ") + path);
+    FileCloser fc{f};
+    FileHeader h{};
+    std::memcpy(h.magic, "VSANNIDX", 8);
+    h.version = FILE_VERSION; h.dims = ix->dims; h.dpad = ix->dpad; h.metric = (uint32_t)ix->metric; h.M = ix->M; h.efA = ix->efA; h.efS = ix->efS;
+    h.n_levels_used = (uint32_t)top_for(ix, ix->n_slots) + 1; h.n_slots = ix->n_slots; h.live = ix->live; h.max_batch = ix->max_batch;
+    Summer sum; sum.add(&h, sizeof h);
+    if (fwrite(&h, sizeof h, 1, f) != 1) return fail(VS_ERR_INVALID, "save: short write");
+    std::vector<unsigned char> buf(64u << 20);
+    const size_t n = ix->n_slots;
+    if ((s = dump(f, sum, ix->vecs, n * ix->dpad * 4, buf)) != VS_OK) return s;
+    if ((s = dump(f, sum, ix->sqn, n * 4, buf)) != VS_OK) return s;
+    if ((s = dump(f, sum, ix->links0, n * ix->W0 * 4, buf)) != VS_OK) return s;
+    for (uint32_t l = 1; l < h.n_levels_used; ++l) {
+        const size_t nr = (n + ix->stride[l] - 1) / ix->stride[l];
+        if ((s = dump(f, sum, ix->linksU[l], nr * ix->M * 4, buf)) != VS_OK) return s;
+    }
+    if ((s = dump(f, sum, ix->slot_key, n * 8, buf)) != VS_OK) return s;
+    if ((s = dump(f, sum, ix->deleted, ((n + 31) / 32) * 4, buf)) != VS_OK) return s;
+    if (fwrite(&sum.h, 8, 1, f) != 1 || fflush(f) != 0) return fail(VS_ERR_INVALID, "save: short write");
+    return VS_OK;
+}
+
+vs_status vs_index_load(const char* path, const vs_options* ov, vs_index** out) {
+    if (!path || !out) return fail(VS_ERR_INVALID, "load: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(VS_ERR_INVALID, std::string("load: cannot open ") + path);
+    FileCloser fc{f};
+    FileHeader h{};
+    if (fread(&h, sizeof h, 1, f) != 1 || std::memcmp(h.magic, "VSANNIDX", 8) != 0) return fail(VS_ERR_INVALID, "load: not a vsann index file");
+    if (h.version > FILE_VERSION) return fail(VS_ERR_UNSUPPORTED, "load: file format " + std::to_string(h.version) + " is newer than this library");
+    if (h.version == 0 || h.dims == 0 || h.dpad != ((h.dims + 3u) & ~3u) || h.metric > 2 || h.M < 2 || h.M > 16 || h.n_slots >= 0x7FFFFFF0ull || h.live > h.n_slots)
+        return fail(VS_ERR_INVALID, "load: corrupt header");
+    vs_options o{};
+    o.dims = h.dims; o.metric = (int)h.metric; o.connectivity = h.M; o.expansion_add = h.efA; o.expansion_search = h.efS;
+    o.device = ov ? ov->device : 0; o.max_batch = ov && ov->max_batch ? ov->max_batch : h.max_batch;
+    const size_t hint = ov && ov->capacity_hint ? ov->capacity_hint : 1000000;
+    o.capacity_hint = hint;
+    vs_index* ix = nullptr;
+    vs_status s = vs_index_create(&o, &ix); if (s != VS_OK) return s;
+    auto body = [&]() -> vs_status {
+        std::lock_guard<std::mutex> g(ix->mu);
+        const size_t n = (size_t)h.n_slots;
+        vs_status r = do_reserve(ix, n + std::max<size_t>(hint / 3, 1)); if (r != VS_OK) return r;
+        if ((uint32_t)top_for(ix, (uint32_t)n) + 1 != h.n_levels_used) return fail(VS_ERR_INVALID, "load: level count does not match the slot count");
+        Summer sum; sum.add(&h, sizeof h);
+        std::vector<unsigned char> buf(64u << 20);
+        if ((r = restore(f, sum, ix->vecs, n * ix->dpad * 4, buf)) != VS_OK) return r;
+        if ((r = restore(f, sum, ix->sqn, n * 4, buf)) != VS_OK) return r;
+        if ((r = restore(f, sum, ix->links0, n * ix->W0 * 4, buf)) != VS_OK) return r;
+        for (uint32_t l = 1; l < h.n_levels_used; ++l) {
+            const size_t nr = (n + ix->stride[l] - 1) / ix->stride[l];
+            if ((r = restore(f, sum, ix->linksU[l], nr * ix->M * 4, buf)) != VS_OK) return r;
+        }
+        // slot keys and tombstones are also needed on the host: key -> newest live slot
+        std::vector<uint64_t> keys(n); std::vector<uint32_t> del((n + 31) / 32);
+        if (n && fread(keys.data(), 8, n, f) != n) return fail(VS_ERR_INVALID, "load: file is truncated");
+        sum.add(keys.data(), n * 8);
+        if (n && fread(del.data(), 4, del.size(), f) != del.size()) return fail(VS_ERR_INVALID, "load: file is truncated");
+        sum.add(del.data(), del.size() * 4);
+        uint64_t want = 0;
+        if (fread(&want, 8, 1, f) != 1) return fail(VS_ERR_INVALID, "load: file is truncated");
+        if (want != sum.h) return fail(VS_ERR_INVALID, "load: checksum mismatch");
+        if (n) { CU(cudaMemcpy(ix->slot_key, keys.data(), n * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(ix->deleted, del.data(), del.size() * 4, cudaMemcpyHostToDevice)); }
+        size_t live = 0;
+        ix->key_slot.reserve(h.live * 2);
+        for (size_t sl = 0; sl < n; ++sl) {
+            ix->host_slot_key[sl] = keys[sl];
+            if (del[sl >> 5] >> (sl & 31) & 1u) continue;
+            if (!ix->key_slot.emplace(keys[sl], (uint32_t)sl).second) return fail(VS_ERR_INVALID, "load: two live slots share a key");
+            ++live;
+        }
+        if (live != h.live) return fail(VS_ERR_INVALID, "load: live count does not match the tombstones");
+        ix->n_slots = (uint32_t)n; ix->live = live; ix->top_level = top_for(ix, ix->n_slots);
+        return VS_OK;
+    };
+    s = body();
+    if (s != VS_OK) { std::string keep = g_err; vs_index_destroy(ix); g_err = keep; return s; }
+    *out = ix; return VS_OK;
 }
 
 const char* vs_last_error(void) { return g_err.c_str(); }
