@@ -426,7 +426,7 @@ def main():
                       "batches": st["build_batches"], "unit": "vectors/s"},
             "e2e": {"value": shard_q / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * D * 4, "d2h_bytes_per_step": nq * K_NN * 12,
                     "ms_per_step": e2e_ms, "recall_at_10": e2e_recall},
-            "gpu_launches": args.steps,
+            "gpu_launches": args.steps * (1 if world == 1 else 2),   # per step: k_search_t (+ k_merge_topk after the all-gather)
             "exact": exact,
             "roofline": {"bound": "hbm", "kernel": "k_search_t", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel_ms": ms_kernel,
