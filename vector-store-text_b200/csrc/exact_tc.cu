@@ -364,14 +364,14 @@ struct RerankArgs {
 __global__ void __launch_bounds__(128) k_tc_exact_dist(RerankArgs a) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t q = blockIdx.y;
+    const uint32_t q = blockIdx.x, cblk = blockIdx.y;   // queries on x: batches above 65535 queries
     const uint32_t cnt = min(a.cnt[q], a.cap);
-    if (blockIdx.x * 128u >= cnt) return;                          // whole block past the end
+    if (cblk * 128u >= cnt) return;                          // whole block past the end
     float* qs = reinterpret_cast<float*>(sm);
     float* tile = qs + a.dpad + (size_t)warp * 32 * 33;
     for (uint32_t c = threadIdx.x; c < a.dpad; c += blockDim.x) qs[c] = a.q[(size_t)q * a.q_stride + c];
     __syncthreads();
-    const uint32_t b0 = (blockIdx.x * 4 + warp) * 32;
+    const uint32_t b0 = (cblk * 4 + warp) * 32;
     if (b0 >= cnt) return;
     uint32_t slot = b0 + lane < cnt ? a.cand[(size_t)q * a.cap + b0 + lane] : NONE;
     if (slot != NONE && a.deleted && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) slot = NONE;
@@ -596,7 +596,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     r.cand = S.cand; r.cand_d = S.cand_d; r.cnt = S.cnt; r.tau = S.tau; r.max_xn_bits = S.ctr + 1; r.out_keys = out_keys; r.out_slots = out_slots; r.out_dist = out_dist; r.out_ld = out_ld;
     r.self_first = q.self_first; r.self_step = q.self_step;
     r.n_r2 = S.ctr; r.r2_ids = S.r2_ids; r.r2_tau = S.r2_tau; r.r2_qn = S.r2_qn; r.n_fb = S.ctr + 2; r.fb_ids = S.fb_ids;
-    k_tc_exact_dist<<<dim3((p.cap + 127) / 128, q.nq), 128, dsmem, st>>>(r);
+    k_tc_exact_dist<<<dim3(q.nq, (p.cap + 127) / 128), 128, dsmem, st>>>(r);
     auto select = [&](const RerankArgs& ra, uint32_t nqs) {
         if (c.slot_key) k_tc_select<LessByKey><<<(nqs + 3) / 4, 128, ssmem, st>>>(ra, LessByKey{c.slot_key, c.n_slots});
         else k_tc_select<LessById><<<(nqs + 3) / 4, 128, ssmem, st>>>(ra, LessById());
@@ -624,7 +624,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
         k_tc_scan<true><<<dim3(p2.nqt, p2.slices), THREADS, SMEM_BYTES, st>>>(mapQ2, mapX, a2);
         RerankArgs r2 = r;
         r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = n2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr;
-        k_tc_exact_dist<<<dim3((p.cap + 127) / 128, n2), 128, dsmem, st>>>(r2);
+        k_tc_exact_dist<<<dim3(n2, (p.cap + 127) / 128), 128, dsmem, st>>>(r2);
         select(r2, n2);
         TC_TRY(cudaGetLastError());
         TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));

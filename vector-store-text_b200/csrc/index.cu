@@ -83,6 +83,7 @@ struct vs_index {
     std::vector<uint64_t> pend_keys; std::vector<float> pend_vecs; std::unordered_map<uint64_t, size_t> pend_pos;
     std::vector<uint64_t> host_slot_key;
     uint64_t st_build_vectors = 0, st_build_batches = 0; double st_build_seconds = 0; size_t device_bytes = 0;
+    bool build_trace = false; std::vector<cudaEvent_t> trace_ev;   // VSANN_BUILD_TRACE=1: four events per batch (start, search, batch-knn, link)
 
     GraphView view(uint32_t visible, int top) const {
         GraphView g{};
@@ -204,8 +205,11 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
     }
     b.item_off[MAX_LEVELS] = off; b.total_items = off;
     unsigned long long* ctr = ix->stats_on ? ix->counters : nullptr;
+    auto mark = [&]() { if (ix->build_trace) { cudaEvent_t e; if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ix->stream); ix->trace_ev.push_back(e); } } };
+    mark();
     GraphView frozen = ix->view(first, b.new_top);
     CU(launch_build_search(frozen, b, ix->efA, ix->dev, ctr, ix->stream));
+    mark();
     for (int l = 0; l <= b.new_top; ++l) {
         if (b.items[l] < 2) { b.knn_id[l] = nullptr; b.knn_d[l] = nullptr; continue; }
         const uint32_t s = ix->stride[l], fs = b.first_row[l] * s;
@@ -215,16 +219,23 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         const uint32_t k = std::min<uint32_t>(KNN_BATCH, b.items[l] - 1);
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
         if (ix->build_tc && exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
-            CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count)));
+            size_t want = exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count);
+            if (want > ix->tc_scratch.n) {   // size it once for every batch shape up to max_batch: a cudaFree + cudaMalloc per growing batch cost up to 300 ms
+                for (uint32_t b = 4096; b <= ix->max_batch; b *= 2) want = std::max(want, exact_tc_scratch_bytes(b, b, KNN_BATCH + 1, ix->dpad, ix->dev.sm_count));
+                want = std::max(want, exact_tc_scratch_bytes(ix->max_batch, ix->max_batch, KNN_BATCH + 1, ix->dpad, ix->dev.sm_count));
+            }
+            CU(ix->tc_scratch.ensure(want));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
             CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, &ix->tc_build_stats));
             continue;
         }
         CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ix->stream));
     }
+    mark();
     CU(cudaMemsetAsync(ix->lt.n_edges, 0, 8, ix->stream));
     GraphView linked = ix->view(first + count, b.new_top);
     CU(launch_link(linked, b, ix->lt, ix->efpA, KNN_BATCH, ix->dev, ctr, ix->stream));
+    mark();
     ix->st_build_batches++;
     return VS_OK;
 }
@@ -275,6 +286,21 @@ vs_status flush_locked(vs_index* ix, const float* d_rows /* device rows or null 
     CU(cudaEventRecord(ix->ev1, ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
     float ms = 0; cudaEventElapsedTime(&ms, ix->ev0, ix->ev1); ix->st_build_seconds += ms * 1e-3;
+    if (ix->build_trace && !ix->trace_ev.empty()) {   // per-phase device time and the gaps between batches
+        double ph[3] = {0, 0, 0}, gaps = 0, worst = 0; size_t worst_i = 0;
+        const size_t nb = ix->trace_ev.size() / 4;
+        for (size_t i = 0; i < nb; ++i) {
+            float t;
+            for (int k = 0; k < 3; ++k) { cudaEventElapsedTime(&t, ix->trace_ev[4 * i + k], ix->trace_ev[4 * i + k + 1]); ph[k] += t; }
+            cudaEventElapsedTime(&t, ix->trace_ev[4 * i], ix->trace_ev[4 * i + 3]);
+            if (t > worst) { worst = t; worst_i = i; }
+            if (i + 1 < nb) { cudaEventElapsedTime(&t, ix->trace_ev[4 * i + 3], ix->trace_ev[4 * i + 4]); gaps += t; }
+        }
+        fprintf(stderr, "[vsann build trace] %zu batches: total %.1f ms = search %.1f + batch-knn %.1f + link %.1f + gaps %.1f; slowest batch #%zu %.2f ms\n",
+                nb, ms, ph[0], ph[1], ph[2], gaps, worst_i, worst);
+        for (cudaEvent_t e : ix->trace_ev) cudaEventDestroy(e);
+        ix->trace_ev.clear();
+    }
     ix->n_slots = base + (uint32_t)n; ix->live += n; ix->top_level = top_for(ix, ix->n_slots);
     ix->st_build_vectors += n;
     if (!from_dev) { ix->pend_keys.clear(); ix->pend_vecs.clear(); ix->pend_pos.clear(); }
@@ -353,6 +379,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_STAGE_BYTES")) ix->dev.stage_bytes = (uint32_t)atol(e);
     if (const char* e = getenv("VSANN_GATHER4")) ix->dev.gather4 = atoi(e) != 0;
     if (const char* e = getenv("VSANN_ZERO_COPY")) ix->zero_copy = atoi(e) != 0;   // 0: always stage host queries with a copy
+    if (const char* e = getenv("VSANN_BUILD_TRACE")) ix->build_trace = atoi(e) != 0;   // per-phase build timing on stderr
     if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
     vs_status s = VS_OK;
     auto body = [&]() -> vs_status {
