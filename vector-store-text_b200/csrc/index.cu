@@ -66,7 +66,7 @@ struct vs_index {
     // options
     uint32_t dims = 0, dpad = 0; int metric = 0; uint32_t M = 16, W0 = 32, efA = 128, efS = 64;
     uint32_t max_batch = 16384, batch_div = 16; size_t reserve_increment = 1000000;
-    DeviceInfo dev; cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, user_ev = nullptr; bool user_pending = false;
+    DeviceInfo dev; cudaStream_t stream = nullptr, side = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, user_ev = nullptr, fork_ev = nullptr, join_ev = nullptr; bool user_pending = false, build_overlap = true;
     std::mutex mu;
     // tables
     size_t capacity = 0; uint32_t n_slots = 0; size_t live = 0; int top_level = 0; int n_levels = 1;
@@ -207,6 +207,10 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
     unsigned long long* ctr = ix->stats_on ? ix->counters : nullptr;
     auto mark = [&]() { if (ix->build_trace) { cudaEvent_t e; if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ix->stream); ix->trace_ev.push_back(e); } } };
     mark();
+    // The graph search of the batch (K4a, frozen graph) and its exact intra-batch neighbours (K1/K2/K1f) are independent:
+    // they run on two streams and join before the link step.
+    cudaStream_t ks = ix->build_overlap ? ix->side : ix->stream;
+    if (ix->build_overlap) { CU(cudaEventRecord(ix->fork_ev, ix->stream)); CU(cudaStreamWaitEvent(ks, ix->fork_ev, 0)); }
     GraphView frozen = ix->view(first, b.new_top);
     CU(launch_build_search(frozen, b, ix->efA, ix->dev, ctr, ix->stream));
     mark();
@@ -226,11 +230,12 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
             }
             CU(ix->tc_scratch.ensure(want));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
-            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ix->stream, &ix->tc_build_stats));
+            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ks, &ix->tc_build_stats));
             continue;
         }
-        CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ix->stream));
+        CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ks));
     }
+    if (ix->build_overlap) { CU(cudaEventRecord(ix->join_ev, ks)); CU(cudaStreamWaitEvent(ix->stream, ix->join_ev, 0)); }
     mark();
     CU(cudaMemsetAsync(ix->lt.n_edges, 0, 8, ix->stream));
     GraphView linked = ix->view(first + count, b.new_top);
@@ -379,11 +384,14 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_STAGE_BYTES")) ix->dev.stage_bytes = (uint32_t)atol(e);
     if (const char* e = getenv("VSANN_GATHER4")) ix->dev.gather4 = atoi(e) != 0;
     if (const char* e = getenv("VSANN_ZERO_COPY")) ix->zero_copy = atoi(e) != 0;   // 0: always stage host queries with a copy
+    if (const char* e = getenv("VSANN_BUILD_OVERLAP")) ix->build_overlap = atoi(e) != 0;   // 0: batch neighbours after the graph search, same stream
     if (const char* e = getenv("VSANN_BUILD_TRACE")) ix->build_trace = atoi(e) != 0;   // per-phase build timing on stderr
     if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
     vs_status s = VS_OK;
     auto body = [&]() -> vs_status {
         CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&ix->side, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&ix->fork_ev, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ix->join_ev, cudaEventDisableTiming));
         CU(cudaEventCreate(&ix->ev0)); CU(cudaEventCreate(&ix->ev1)); CU(cudaEventCreateWithFlags(&ix->user_ev, cudaEventDisableTiming));
         CU(cudaMalloc(&ix->counters, 8 * sizeof(unsigned long long)));
         CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
@@ -408,6 +416,8 @@ void vs_index_destroy(vs_index* ix) {
     ix->build_scratch.release(); ix->exact_scratch.release(); ix->tc_scratch.release(); ix->stage.release(); ix->tomb.release();
     ix->qpad.release(); ix->qdense.release(); ix->out_d.release(); ix->out_k.release();
     if (ix->ev0) cudaEventDestroy(ix->ev0); if (ix->ev1) cudaEventDestroy(ix->ev1); if (ix->user_ev) cudaEventDestroy(ix->user_ev);
+    if (ix->fork_ev) cudaEventDestroy(ix->fork_ev); if (ix->join_ev) cudaEventDestroy(ix->join_ev);
+    if (ix->side) { cudaStreamSynchronize(ix->side); cudaStreamDestroy(ix->side); }
     if (ix->stream) cudaStreamDestroy(ix->stream);
     cudaGetLastError();
     delete ix;
