@@ -6,8 +6,8 @@
 // dependent rounds of register loads: a warp keeps up to `rows` x row_bytes in flight without
 // holding them in registers, so a beam step costs two dependent memory round trips (link row,
 // then all vectors) and the link row of every accepted candidate is prefetched into L2 as soon
-// as it is accepted. Distances use the accumulation order of warp_dist32 (8-lane teams, chunk
-// c = tl + 8 i, xor-4/2/1 reduction), so both paths return identical bits.
+// as it is accepted. Distances: 8-lane teams, chunk c = tl + 8 i per lane on the packed-f32 pipe (even / odd
+// partial sums), xor-4/2/1 reduction; within 1e-6 relative of warp_dist32's scalar chain, not the same bits.
 #pragma once
 #include <cuda.h>
 #include "rbeam.cuh"
@@ -100,15 +100,21 @@ struct QRegs {
     }
 };
 
+// One 16-byte chunk of a row against the query chunk, on Blackwell's packed-f32 pipe (FFMA2: two independent f32
+// FMAs per instruction, each rounded like a scalar fmaf). The accumulator is a pair: .x sums the even components,
+// .y the odd ones; the lane's partial sum is acc.x + acc.y. L2: t = q - x is formed as fma(x, -1, q) (exact product,
+// one rounding: the same value as the subtraction).
 template <int METRIC>
-__device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, float& acc) {
+__device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, float2& acc) {
     if (METRIC == L2SQ) {
-        float t;
-        t = q.x - x.x; acc = fmaf(t, t, acc); t = q.y - x.y; acc = fmaf(t, t, acc);
-        t = q.z - x.z; acc = fmaf(t, t, acc); t = q.w - x.w; acc = fmaf(t, t, acc);
+        const float2 m1 = make_float2(-1.f, -1.f);
+        const float2 t0 = __ffma2_rn(make_float2(x.x, x.y), m1, make_float2(q.x, q.y));
+        const float2 t1 = __ffma2_rn(make_float2(x.z, x.w), m1, make_float2(q.z, q.w));
+        acc = __ffma2_rn(t0, t0, acc);
+        acc = __ffma2_rn(t1, t1, acc);
     } else {
-        acc = fmaf(q.x, x.x, acc); acc = fmaf(q.y, x.y, acc);
-        acc = fmaf(q.z, x.z, acc); acc = fmaf(q.w, x.w, acc);
+        acc = __ffma2_rn(make_float2(q.x, q.y), make_float2(x.x, x.y), acc);
+        acc = __ffma2_rn(make_float2(q.z, q.w), make_float2(x.z, x.w), acc);
     }
 }
 
@@ -154,17 +160,18 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
         mbar_wait(T.bar + 8u * (uint32_t)slot, (T.parity >> slot) & 1u); T.parity ^= 1u << slot;
         const int j = 4 * grp + (int)team;
         const float4* x4 = reinterpret_cast<const float4*>(T.buf + ((size_t)slot * 4u + team) * T.row_bytes);
-        float acc = 0.f;
+        float2 acc2 = make_float2(0.f, 0.f);
         if (CPL > 0) {
             float4 x[CPL > 0 ? CPL : 1];
 #pragma unroll
             for (int i = 0; i < CPL; ++i) x[i] = x4[tl + 8 * i];
 #pragma unroll
-            for (int i = 0; i < CPL; ++i) acc_chunk<METRIC>(Q.v[i], x[i], acc);
+            for (int i = 0; i < CPL; ++i) acc_chunk<METRIC>(Q.v[i], x[i], acc2);
         } else {
 #pragma unroll 4
-            for (int c = tl; c < chunks; c += 8) acc_chunk<METRIC>(S.q4[c], x4[c], acc);
+            for (int c = tl; c < chunks; c += 8) acc_chunk<METRIC>(S.q4[c], x4[c], acc2);
         }
+        float acc = acc2.x + acc2.y;
 #pragma unroll
         for (int o = 4; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (tl == 0 && j < nvalid) S.scr_d[j] = finish_metric(METRIC, acc, qn, METRIC == COS ? S.scr_d[j] : 0.f);
