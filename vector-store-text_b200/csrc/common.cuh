@@ -55,6 +55,24 @@ __device__ __forceinline__ float finish_metric(int metric, float acc, float qn, 
     return 1.f - acc / (sqrtf(qn) * sqrtf(vn));
 }
 
+// One 16-byte chunk of a row against the query chunk, on Blackwell's packed-f32 pipe (FFMA2: two independent f32
+// FMAs per instruction, each rounded like a scalar fmaf). The accumulator is a pair: .x sums the even components,
+// .y the odd ones; the lane's partial sum is acc.x + acc.y. L2: t = q - x is formed as fma(x, -1, q) (exact product,
+// one rounding: the same value as the subtraction).
+template <int METRIC>
+__device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, float2& acc) {
+    if (METRIC == L2SQ) {
+        const float2 m1 = make_float2(-1.f, -1.f);
+        const float2 t0 = __ffma2_rn(make_float2(x.x, x.y), m1, make_float2(q.x, q.y));
+        const float2 t1 = __ffma2_rn(make_float2(x.z, x.w), m1, make_float2(q.z, q.w));
+        acc = __ffma2_rn(t0, t0, acc);
+        acc = __ffma2_rn(t1, t1, acc);
+    } else {
+        acc = __ffma2_rn(make_float2(q.x, q.y), make_float2(x.x, x.y), acc);
+        acc = __ffma2_rn(make_float2(q.z, q.w), make_float2(x.z, x.w), acc);
+    }
+}
+
 // ---- gathered distances --------------------------------------------------------------------
 // One warp evaluates the distance from the query held in shared memory (q4, `chunks` float4s)
 // to up to 32 gathered rows, one id per lane (NONE = skip). Rows are compacted, then teams of
@@ -78,7 +96,7 @@ __device__ __forceinline__ float warp_dist32_m(const GraphView& g, const float4*
         const uint32_t b = j1 < nvalid ? scr_id[j1] : NONE;
         const float4* va = reinterpret_cast<const float4*>(g.vecs + (size_t)(a == NONE ? 0 : a) * g.dpad);
         const float4* vb = reinterpret_cast<const float4*>(g.vecs + (size_t)(b == NONE ? 0 : b) * g.dpad);
-        float acc_a = 0.f, acc_b = 0.f;
+        float2 pa = make_float2(0.f, 0.f), pb = make_float2(0.f, 0.f);
         if (a != NONE) {
 #pragma unroll 4
             for (int c = tl; c < chunks; c += 8) {
@@ -86,20 +104,10 @@ __device__ __forceinline__ float warp_dist32_m(const GraphView& g, const float4*
                 float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (b != NONE) y = ldg_f4(vb + c);
                 const float4 q = q4[c];
-                if (METRIC == L2SQ) {
-                    float t;
-                    t = q.x - x.x; acc_a = fmaf(t, t, acc_a); t = q.y - x.y; acc_a = fmaf(t, t, acc_a);
-                    t = q.z - x.z; acc_a = fmaf(t, t, acc_a); t = q.w - x.w; acc_a = fmaf(t, t, acc_a);
-                    t = q.x - y.x; acc_b = fmaf(t, t, acc_b); t = q.y - y.y; acc_b = fmaf(t, t, acc_b);
-                    t = q.z - y.z; acc_b = fmaf(t, t, acc_b); t = q.w - y.w; acc_b = fmaf(t, t, acc_b);
-                } else {
-                    acc_a = fmaf(q.x, x.x, acc_a); acc_a = fmaf(q.y, x.y, acc_a);
-                    acc_a = fmaf(q.z, x.z, acc_a); acc_a = fmaf(q.w, x.w, acc_a);
-                    acc_b = fmaf(q.x, y.x, acc_b); acc_b = fmaf(q.y, y.y, acc_b);
-                    acc_b = fmaf(q.z, y.z, acc_b); acc_b = fmaf(q.w, y.w, acc_b);
-                }
+                acc_chunk<METRIC>(q, x, pa); acc_chunk<METRIC>(q, y, pb);
             }
         }
+        float acc_a = pa.x + pa.y, acc_b = pb.x + pb.y;
 #pragma unroll
         for (int o = 4; o >= 1; o >>= 1) {
             acc_a += __shfl_xor_sync(0xffffffffu, acc_a, o);

@@ -325,17 +325,64 @@ __device__ __forceinline__ bool heuristic_try(const GraphView& g, WarpSmem& S, K
     return good;
 }
 
+// The same test with the kept rows resident in shared memory (K4b): the candidate row `cq` (shared, landed by a bulk
+// copy) against kept rows 0..kn-1, four at a time (one per 8-lane team), stopping at the first group that holds a
+// closer kept neighbour. Same operand order and summation order as warp_dist32 => the same bits, the same decisions.
+template <int METRIC>
+__device__ __forceinline__ bool kept_any_closer_m(const GraphView& g, const float4* cq, float cn, const float4* kept, int kn,
+                                                  float ksq, float d_base, uint32_t& evals) {
+    const unsigned lane = lane_id(), team = lane >> 3, tl = lane & 7u;
+    const int chunks = g.chunks;
+    for (int jb = 0; jb < kn; jb += 4) {   // warp-uniform trip count
+        const int j = jb + (int)team; const bool on = j < kn;
+        const float4* kr = kept + (size_t)(on ? j : 0) * chunks;
+        float2 acc2 = make_float2(0.f, 0.f);
+#pragma unroll 4
+        for (int c = tl; c < chunks; c += 8) acc_chunk<METRIC>(cq[c], kr[c], acc2);
+        float acc = acc2.x + acc2.y;
+#pragma unroll
+        for (int o = 4; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        const float xn = METRIC == COS ? __shfl_sync(0xffffffffu, ksq, on ? j : 0) : 0.f;
+        const float dk = finish_metric(METRIC, acc, cn, xn);
+        evals += (uint32_t)min(4, kn - jb);
+        if (__ballot_sync(0xffffffffu, on && dk < d_base)) return true;
+    }
+    return false;
+}
+__device__ __forceinline__ bool kept_any_closer(const GraphView& g, const float4* cq, float cn, const float4* kept, int kn,
+                                                float ksq, float d_base, uint32_t& evals) {
+    switch (g.metric) {
+        case L2SQ: return kept_any_closer_m<L2SQ>(g, cq, cn, kept, kn, ksq, d_base, evals);
+        case IP: return kept_any_closer_m<IP>(g, cq, cn, kept, kn, ksq, d_base, evals);
+        default: return kept_any_closer_m<COS>(g, cq, cn, kept, kn, ksq, d_base, evals);
+    }
+}
+// per-warp extra shared memory of the resident-kept-rows path: 2 mbarriers | 2 candidate rows | M kept rows
+__host__ __device__ inline size_t select_extra_bytes(uint32_t dpad, uint32_t M) { return 128 + (size_t)(M + 2) * dpad * 4; }
+
 // ------------------------------------------------- K4b: forward links + reverse-edge inbox ----
 // One warp per (item, level). Merges the graph candidates with the intra-batch kNN candidates
 // (both ascending), runs the heuristic with cap M, writes the item's row, and registers each
 // reverse edge (kept -> item) with the inbox of the kept node's row.
 __global__ void __launch_bounds__(128) k_select(GraphView g, BuildBatch b, LinkTables t, uint32_t efp, uint32_t kbp,
-                                                unsigned long long* counters) {
+                                                unsigned long long* counters, int kept_smem) {
     extern __shared__ __align__(128) unsigned char smem[];
     const unsigned wpb = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = warp_smem_bytes(g.dpad, 32, 32);
     WarpSmem S = carve_warp_smem(smem + warp * per_warp, g.dpad, 32, 32, 32);
     uint32_t evals = 0;
+    // resident-kept-rows path: candidate rows arrive by bulk copy (the next one while the current one is tested)
+    const uint32_t row_bytes = g.dpad * 4u;
+    unsigned char* xb = smem + ((wpb * per_warp + 127) & ~(size_t)127) + warp * select_extra_bytes(g.dpad, g.M);
+    const uint32_t bar_s = smem_u32(xb), cand_s = bar_s + 128u;
+    const float4* cand0 = reinterpret_cast<const float4*>(xb + 128);   // candidate buffer p starts at cand0 + p * chunks
+    float4* kept = reinterpret_cast<float4*>(xb + 128 + 2 * (size_t)row_bytes);
+    uint32_t par = 0;
+    if (kept_smem) {
+        if (lane < 2) mbar_init(bar_s + 8u * lane, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        __syncwarp();
+    }
     for (uint32_t w = blockIdx.x * wpb + warp; w < b.total_items; w += gridDim.x * wpb) {
         int l = 0; while (l + 1 <= b.new_top && w >= b.item_off[l + 1]) ++l;
         const uint32_t idx = w - b.item_off[l];
@@ -348,12 +395,44 @@ __global__ void __launch_bounds__(128) k_select(GraphView g, BuildBatch b, LinkT
         KeepSet K{NONE, 0};
         uint32_t a = 0, c = 0;
         const int cap = (int)g.M;
-        while (K.n < cap && (a < gn || c < bn)) {
+        auto next_cand = [&](uint32_t& id, float& d) -> bool {   // merge of the two ascending candidate lists, skipping the item itself
+            for (;;) {
+                if (!(a < gn || c < bn)) return false;
+                const bool take_g = a < gn && (c >= bn || pair_less(gd[a], gi[a], bd[c], bi[c]));
+                if (take_g) { id = gi[a]; d = gd[a]; ++a; } else { id = bi[c]; d = bd[c]; ++c; }
+                if (id != slot) return true;
+            }
+        };
+        if (kept_smem) {
+            auto fetch = [&](uint32_t id, int p) {
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(bar_s + 8u * p, row_bytes);
+                    bulk_g2s(cand_s + (uint32_t)p * row_bytes, g.vecs + (size_t)id * g.dpad, row_bytes, bar_s + 8u * p);
+                }
+            };
+            uint32_t cur_id = NONE, nxt_id = NONE; float cur_d = 0.f, nxt_d = 0.f, ksq = 0.f; int p = 0;
+            bool have = next_cand(cur_id, cur_d);
+            if (have) fetch(cur_id, p);
+            while (have && K.n < cap) {
+                const bool have_n = next_cand(nxt_id, nxt_d);
+                if (have_n) fetch(nxt_id, p ^ 1);
+                const float cn = g.metric == COS ? g.sqn[cur_id] : 0.f;
+                mbar_wait(bar_s + 8u * p, (par >> p) & 1u); par ^= 1u << p;
+                const bool bad = K.n > 0 && kept_any_closer(g, cand0 + (size_t)p * g.chunks, cn, kept, K.n, ksq, cur_d, evals);
+                if (!bad) {
+                    float4* dst = kept + (size_t)K.n * g.chunks;
+                    for (int ch = lane; ch < (int)g.chunks; ch += 32) dst[ch] = cand0[(size_t)p * g.chunks + ch];
+                    if ((int)lane == K.n) { K.id = cur_id; ksq = cn; }
+                    ++K.n;
+                }
+                __syncwarp();
+                cur_id = nxt_id; cur_d = nxt_d; have = have_n; p ^= 1;
+            }
+            if (have) { mbar_wait(bar_s + 8u * p, (par >> p) & 1u); par ^= 1u << p; }   // the prefetched row nobody needs
+            __syncwarp();
+        } else {
             uint32_t id; float d;
-            const bool take_g = a < gn && (c >= bn || pair_less(gd[a], gi[a], bd[c], bi[c]));
-            if (take_g) { id = gi[a]; d = gd[a]; ++a; } else { id = bi[c]; d = bd[c]; ++c; }
-            if (id == slot) continue;
-            heuristic_try(g, S, K, id, d, evals);
+            while (K.n < cap && next_cand(id, d)) heuristic_try(g, S, K, id, d, evals);
         }
         // forward row
         int width; uint32_t* row = const_cast<uint32_t*>(level_row(g, l, slot, width));
@@ -676,11 +755,14 @@ cudaError_t launch_link(const GraphView& g, const BuildBatch& b, const LinkTable
     if (b.total_items == 0) return cudaSuccess;
     const uint32_t wpb = 4;
     size_t smem = warp_smem_bytes(g.dpad, 32, 32) * wpb;
+    // kept rows resident in shared memory while they fit a 24 KB per-warp budget (d <= 340 at M = 16); else gathers from L1/L2
+    const int kept_smem = dev.select_smem && select_extra_bytes(g.dpad, g.M) <= 24 * 1024;
+    if (kept_smem) smem = ((smem + 127) & ~(size_t)127) + wpb * select_extra_bytes(g.dpad, g.M);
     cudaError_t e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     uint32_t blocks = (b.total_items + wpb - 1) / wpb;
     uint32_t maxb = dev.sm_count * 8; if (blocks > maxb) blocks = maxb;
-    k_select<<<blocks, wpb * 32, smem, st>>>(g, b, t, efp, kbp, counters);
+    k_select<<<blocks, wpb * 32, smem, st>>>(g, b, t, efp, kbp, counters, kept_smem);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     k_inbox_fill<<<dev.sm_count * 4, 256, 0, st>>>(t);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;

@@ -18,6 +18,7 @@ struct DeviceInfo {
     bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)
     uint32_t stage_bytes = 4096;       // per-warp bulk-copy staging area (VSANN_STAGE_BYTES; 0 = register-gather kernels)
     bool gather4 = true;               // TMA tile::gather4 for rows of at most 256 floats (VSANN_GATHER4=0: one bulk copy per row)
+    bool select_smem = true;      // K4b keeps the selected neighbours' rows in shared memory (VSANN_SELECT_SMEM=0: gathers)
     uint32_t* work_ring = nullptr;     // WORK_RING_SLOTS device words: work counters of the persistent kernels
 };
 

@@ -7,7 +7,7 @@
 // holding them in registers, so a beam step costs two dependent memory round trips (link row,
 // then all vectors) and the link row of every accepted candidate is prefetched into L2 as soon
 // as it is accepted. Distances: 8-lane teams, chunk c = tl + 8 i per lane on the packed-f32 pipe (even / odd
-// partial sums), xor-4/2/1 reduction; within 1e-6 relative of warp_dist32's scalar chain, not the same bits.
+// partial sums, acc_chunk in common.cuh), xor-4/2/1 reduction: the same bits as warp_dist32.
 #pragma once
 #include <cuda.h>
 #include "rbeam.cuh"
@@ -99,24 +99,6 @@ struct QRegs {
         for (int i = 0; i < CPL; ++i) v[i] = q4[tl + 8 * i];
     }
 };
-
-// One 16-byte chunk of a row against the query chunk, on Blackwell's packed-f32 pipe (FFMA2: two independent f32
-// FMAs per instruction, each rounded like a scalar fmaf). The accumulator is a pair: .x sums the even components,
-// .y the odd ones; the lane's partial sum is acc.x + acc.y. L2: t = q - x is formed as fma(x, -1, q) (exact product,
-// one rounding: the same value as the subtraction).
-template <int METRIC>
-__device__ __forceinline__ void acc_chunk(const float4& q, const float4& x, float2& acc) {
-    if (METRIC == L2SQ) {
-        const float2 m1 = make_float2(-1.f, -1.f);
-        const float2 t0 = __ffma2_rn(make_float2(x.x, x.y), m1, make_float2(q.x, q.y));
-        const float2 t1 = __ffma2_rn(make_float2(x.z, x.w), m1, make_float2(q.z, q.w));
-        acc = __ffma2_rn(t0, t0, acc);
-        acc = __ffma2_rn(t1, t1, acc);
-    } else {
-        acc = __ffma2_rn(make_float2(q.x, q.y), make_float2(x.x, x.y), acc);
-        acc = __ffma2_rn(make_float2(q.z, q.w), make_float2(x.z, x.w), acc);
-    }
-}
 
 // One group = four rows into staging slot `slot` (4 x row_bytes), completion on that slot's mbarrier. Called by ONE lane.
 // With a tensor map it is a single TMA gather4 (four scattered rows per instruction), else four bulk copies.
