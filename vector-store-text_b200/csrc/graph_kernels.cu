@@ -615,7 +615,7 @@ static inline int vecs_tmap(const GraphView& g, const DeviceInfo& dev, CUtensorM
 }
 static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev) {
     uint32_t hs = next_pow2(ef * dev.hash_factor);
-    if (hs < 1024) hs = 1024;
+    if (hs < dev.hash_min) hs = dev.hash_min;
     if (hs > 16384) hs = 16384;
     return hs;
 }

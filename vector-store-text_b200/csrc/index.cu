@@ -380,6 +380,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     ix->reserve_increment = o->capacity_hint ? o->capacity_hint : 1000000;   // usearch.rs:62
     ix->dev.device = o->device; ix->dev.sm_count = prop.multiProcessorCount; ix->dev.smem_per_block = prop.sharedMemPerBlockOptin;
     if (const char* e = getenv("VSANN_HASH_FACTOR")) { const long v = atol(e); if (v > 0) ix->dev.hash_factor = (uint32_t)v; }
+    if (const char* e = getenv("VSANN_HASH_MIN")) { const long v = atol(e); if (v >= 64) ix->dev.hash_min = (uint32_t)v; }
     if (const char* e = getenv("VSANN_SMEM_LIST")) ix->dev.force_smem_list = atoi(e) != 0;
     if (const char* e = getenv("VSANN_STAGE_BYTES")) ix->dev.stage_bytes = (uint32_t)atol(e);
     if (const char* e = getenv("VSANN_GATHER4")) ix->dev.gather4 = atoi(e) != 0;

@@ -14,7 +14,8 @@ struct DeviceInfo {
     int device = 0;
     int sm_count = 148;
     size_t smem_per_block = 227 * 1024;
-    uint32_t hash_factor = 16;         // visited-hash entries per unit of ef (VSANN_HASH_FACTOR)
+    uint32_t hash_min = 1024;          // smallest visited hash of the staged kernels (VSANN_HASH_MIN)
+    uint32_t hash_factor = 8;          // visited-hash entries per unit of ef (VSANN_HASH_FACTOR); measured: 8 beats 16 (occupancy) and 4 (re-evaluations)
     bool force_smem_list = false;      // VSANN_SMEM_LIST=1: shared-memory list kernel for every ef (A/B testing)
     uint32_t stage_bytes = 4096;       // per-warp bulk-copy staging area (VSANN_STAGE_BYTES; 0 = register-gather kernels)
     bool gather4 = true;               // TMA tile::gather4 for rows of at most 256 floats (VSANN_GATHER4=0: one bulk copy per row)
