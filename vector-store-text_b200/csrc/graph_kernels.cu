@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(const __grid_con
     WarpSmem S; WarpStage T;
     carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
     if (use_vmap) T.tmap = &vmap;
+    T.pf_over = true;
     uint32_t evals = 0, exps = 0, done = 0;
     for (;;) {   // persistent warps: every warp draws its next query from a device counter (no tail, no intra-block wait)
         uint32_t q = 0;

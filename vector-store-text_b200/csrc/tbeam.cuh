@@ -45,6 +45,21 @@ __device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap* map
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(0), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
 }
+// one instruction brings `bytes` (multiple of 16) into L2; nothing is waited for
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+// read-only probe of the visited hash (same probe sequence as visited_test_set)
+__device__ __forceinline__ bool visited_probe(const uint32_t* hs, uint32_t hmask, uint32_t id) {
+    const uint32_t h = (id * 0x9E3779B1u) >> 7;
+#pragma unroll 1
+    for (int probe = 0; probe < 8; ++probe) {
+        const uint32_t v = hs[(h + probe) & hmask];
+        if (v == id) return true;
+        if (v == NONE) return false;
+    }
+    return false;
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) {
 #ifndef VSANN_NO_PREFETCH
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
@@ -54,6 +69,13 @@ __device__ __forceinline__ void prefetch_l2(const void* p) {
 // rows longer than this use cp.async.bulk, shorter ones LDGSTS. Measured on B200 (1M x 128, ef=24):
 // bulk 11.4M QPS vs LDGSTS 9.6M QPS, so every row goes through the bulk path.
 constexpr uint32_t BULK_MIN_ROW_BYTES = 0;
+#ifndef VSANN_PF_NEXT
+#define VSANN_PF_NEXT 0
+#endif
+// L2 prefetch (UBLKPF) of the likely next node's unvisited neighbours while the current gather is in flight. Measured on
+// B200 (1M x 128, ef=24): 13.7M QPS with it vs 15.2M without, and slower even for a single wave of queries (0.408 vs
+// 0.377 ms at 2500 queries): the probe + prefetch issue costs more than the L2 hits return. Off.
+constexpr bool PF_NEXT = VSANN_PF_NEXT != 0;
 
 struct WarpStage {
     const unsigned char* buf;   // rows x row_bytes staging area (generic pointer)
@@ -63,6 +85,7 @@ struct WarpStage {
     uint32_t rows;              // staging capacity in rows (a multiple of 4)
     uint32_t row_bytes;         // dpad * 4
     const CUtensorMap* tmap;    // vecs as a [slots][dpad] tensor with a one-row box (null: rows longer than a TMA box)
+    bool pf_over;               // L2-prefetch the rows of an expansion that do not fit the staging area
 };
 
 // per-warp layout: query | scr_id[32] | scr_d[32] | 8 mbarriers (one per staging slot of four rows) | visited hash | staging rows (128 B aligned)
@@ -82,7 +105,7 @@ __device__ __forceinline__ void carve_tsmem(unsigned char* base, uint32_t dpad, 
     S.hmask = hsize - 1;
     p = base + ((((size_t)(p - base)) + 127) & ~(size_t)127);
     T.buf = p; T.buf_s = smem_u32(p);
-    T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0; T.tmap = nullptr;
+    T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0; T.tmap = nullptr; T.pf_over = false;
     S.L.ld = S.L.ld2 = nullptr; S.L.li = S.L.li2 = nullptr; S.L.cap = S.L.capp = 0;
     if (lane_id() < 8) mbar_init(T.bar + 8u * lane_id(), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -122,10 +145,13 @@ __device__ __forceinline__ void stage_issue_group(const GraphView& g, const Warp
 // so an expansion with more rows than the staging area holds pays the memory latency once, not once per refill.
 template <int METRIC, int CPL>
 __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
-                                                uint32_t id, uint32_t& n_evals) {
+                                                uint32_t id, uint32_t& n_evals, uint32_t pf = NONE) {
     const unsigned lane = lane_id(), team = lane >> 3, tl = lane & 7u;
     const unsigned valid = __ballot_sync(0xffffffffu, id != NONE);
-    if (valid == 0u) return INFINITY;
+    if (valid == 0u) {
+        if (pf != NONE && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
+        return INFINITY;
+    }
     const int nvalid = __popc(valid);
     const int pos = __popc(valid & ((1u << lane) - 1u));
     const uint32_t first = __shfl_sync(0xffffffffu, id, __ffs(valid) - 1);
@@ -136,6 +162,11 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
     const int chunks = g.chunks;
     const int ngroups = (nvalid + 3) >> 2, ns = (int)(T.rows >> 2);
     if ((int)lane < min(ns, ngroups)) stage_issue_group(g, S, T, (int)lane, (int)lane);
+    // rows beyond the staging capacity wait for a free slot: have them in L2 by then (they are needed for certain).
+    // Measured on B200: search 15.15M -> 15.73M QPS; the build search (ef_add wide, mostly L2-resident) loses 2 %, so it is per kernel.
+    if (T.pf_over && (int)lane >= (int)T.rows && (int)lane < nvalid) bulk_prefetch_l2(g.vecs + (size_t)S.scr_id[lane] * g.dpad, T.row_bytes);
+    // while this expansion's rows are in flight: bring the not yet visited neighbours of the likely next node into L2
+    if (pf != NONE && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
     if (METRIC == COS) { if (id != NONE) S.scr_d[pos] = g.sqn[id]; __syncwarp(); }
     int slot = 0;
     for (int grp = 0; grp < ngroups; ++grp) {
@@ -168,11 +199,11 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
 
 template <int CPL>
 __device__ __forceinline__ float stage_dist32(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn,
-                                              uint32_t id, uint32_t& n_evals) {
+                                              uint32_t id, uint32_t& n_evals, uint32_t pf = NONE) {
     switch (g.metric) {
-        case L2SQ: return stage_dist32_m<L2SQ, CPL>(g, S, T, Q, qn, id, n_evals);
-        case IP: return stage_dist32_m<IP, CPL>(g, S, T, Q, qn, id, n_evals);
-        default: return stage_dist32_m<COS, CPL>(g, S, T, Q, qn, id, n_evals);
+        case L2SQ: return stage_dist32_m<L2SQ, CPL>(g, S, T, Q, qn, id, n_evals, pf);
+        case IP: return stage_dist32_m<IP, CPL>(g, S, T, Q, qn, id, n_evals, pf);
+        default: return stage_dist32_m<COS, CPL>(g, S, T, Q, qn, id, n_evals, pf);
     }
 }
 
@@ -234,7 +265,7 @@ __device__ __forceinline__ void tbeam_level(const GraphView& g, int level, WarpS
             if (nb != NONE && nb >= g.n_slots) nb = NONE;
             if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
             __syncwarp();
-            const float d = stage_dist32<CPL>(g, S, T, Q, qn, nb, evals);
+            const float d = stage_dist32<CPL>(g, S, T, Q, qn, nb, evals, PF_NEXT && spec_id != NONE ? spec_nb : NONE);
             const bool good = nb != NONE && d < L.worst;
             if (good) { int w2; prefetch_l2(level_row(g, level, nb, w2)); }   // it may be expanded later: have its links in L2
             unsigned acc = __ballot_sync(0xffffffffu, good);
