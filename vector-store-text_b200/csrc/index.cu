@@ -65,7 +65,7 @@ template <class T> struct DBuf {
 struct vs_index {
     // options
     uint32_t dims = 0, dpad = 0; int metric = 0; uint32_t M = 16, W0 = 32, efA = 128, efS = 64;
-    uint32_t max_batch = 16384, batch_div = 16; size_t reserve_increment = 1000000;
+    uint32_t max_batch = 32768, batch_div = 16; size_t reserve_increment = 1000000;
     DeviceInfo dev; cudaStream_t stream = nullptr, side = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, user_ev = nullptr, fork_ev = nullptr, join_ev = nullptr; bool user_pending = false, build_overlap = true;
     std::mutex mu;
     // tables
@@ -373,7 +373,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     ix->M = (uint32_t)M; ix->W0 = 2 * ix->M;
     ix->efA = (uint32_t)(o->expansion_add ? o->expansion_add : 128);
     ix->efS = (uint32_t)(o->expansion_search ? o->expansion_search : 64);
-    ix->max_batch = (uint32_t)(o->max_batch ? o->max_batch : 16384);
+    ix->max_batch = (uint32_t)(o->max_batch ? o->max_batch : 32768);
     if (const char* e = getenv("VSANN_MAX_BATCH")) { const long v = atol(e); if (v > 0) ix->max_batch = (uint32_t)v; }
     if (ix->max_batch < 32) ix->max_batch = 32;
     if (const char* e = getenv("VSANN_BATCH_DIV")) { const long v = atol(e); if (v > 0) ix->batch_div = (uint32_t)v; }
