@@ -64,35 +64,123 @@ def recall(found, truth):
     return hit / truth.size
 
 
-class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+_POLLER = r"""
+import os, subprocess, sys, time
+gpu, uuid, out = int(sys.argv[1]), sys.argv[2], open(sys.argv[3], "w", buffering=1)
+Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+try:
+    import pynvml as nv
+    nv.nvmlInit()
+    h = None
+    for u in ([uuid, "GPU-" + uuid] if uuid else []):
+        try:
+            h = nv.nvmlDeviceGetHandleByUUID(u); break
+        except Exception:
+            h = None
+    if h is None:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        tok = vis.split(",")[gpu].strip() if vis else str(gpu)
+        h = nv.nvmlDeviceGetHandleByIndex(int(tok)) if tok.isdigit() else nv.nvmlDeviceGetHandleByUUID(tok)
+    mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+    reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+    masks = (0x8, 0x40, 0x20, 0x4)   # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap (nvml.h)
+    out.write("# nvml %d\n" % mx)
+    while True:
+        mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+        try:
+            b = int(reasons(h))
+        except Exception:
+            b = 0
+        out.write("%.6f,%d,%d,%d,%d,%d\n" % ((time.time(), mhz) + tuple(1 if b & m else 0 for m in masks)))
+        time.sleep(0.001)
+except Exception as e:
+    out.write("# nvidia-smi (nvml failed: %s)\n" % (str(e)[:80],))
+    p = subprocess.Popen(["nvidia-smi", "-i", str(gpu), "--query-gpu=" + Q, "--format=csv,noheader,nounits", "-lms", "20"],
+                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+    for line in p.stdout:
+        c = [v.strip() for v in line.split(",")]
+        if len(c) >= 6 and c[0].replace(".", "").isdigit():
+            out.write("%.6f,%s,%s,%s,%s,%s,%s\n" % ((time.time(), c[0]) + tuple("1" if v.lower().startswith("active") else "0" for v in c[2:6]) + (c[1],)))
+"""
 
-    def __init__(self, gpu):
-        self.gpu, self.rows, self.proc = gpu, [], None
+
+class ClockSampler:
+    """SM clocks + throttle reasons under load (B200_PROFILING.md clocks line). The timed regions are a few
+    milliseconds long, shorter than one `nvidia-smi -lms` period, so a separate process (no GIL shared with the
+    timed loop) polls NVML every millisecond and timestamps each sample; `mark(True/False)` records the wall-clock
+    windows of the timed regions and the medians are taken over the samples that fell inside them. When NVML cannot
+    be loaded the poller falls back to `nvidia-smi -lms 20`, and bench.py keeps the timed step itself running until
+    a few samples have arrived (`need_tail`)."""
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, gpu, uuid=None):
+        self.gpu, self.uuid, self.proc, self.path = gpu, uuid or "", None, None
+        self.windows, self.t_open = [], None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import tempfile
+            fd, self.path = tempfile.mkstemp(prefix="vsann_clocks_", suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen([sys.executable, "-c", _POLLER, str(self.gpu), self.uuid, self.path],
+                                         stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def mark(self, inside):
+        if inside:
+            self.t_open = time.time()
+        elif self.t_open is not None:
+            self.windows.append((self.t_open, time.time()))
+            self.t_open = None
+
+    def _parse(self):
+        rows, source, mx = [], None, None
+        try:
+            for line in open(self.path):
+                if line.startswith("#"):
+                    tok = line[1:].split()
+                    source = tok[0]
+                    if source == "nvml" and len(tok) > 1:
+                        mx = float(tok[1])
+                    continue
+                c = line.strip().split(",")
+                if len(c) < 6:
+                    continue
+                t, mhz = float(c[0]), float(c[1])
+                if len(c) > 6 and c[6].replace(".", "").isdigit():
+                    mx = max(mx or 0.0, float(c[6]))
+                inside = any(a <= t <= b for a, b in self.windows) or (self.t_open is not None and t >= self.t_open)
+                rows.append((mhz, [self.NAMES[i] for i in range(4) if c[2 + i] == "1"], inside))
+        except Exception:
+            pass
+        return rows, source, mx
+
+    def need_tail(self, want=3):
+        """True while fewer than `want` samples fell inside a timed region (only the nvidia-smi fallback is that slow)."""
+        if self.proc is None:
+            return False
+        return sum(1 for r in self._parse()[0] if r[2]) < want
 
     def stop(self):
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock poller could not be started"], "samples": 0}
         self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        rows, source, mx = self._parse()
+        try:
+            os.unlink(self.path)
+        except Exception:
+            pass
+        ins = [r for r in rows if r[2]]
+        use = ins if ins else rows
+        sm = [r[0] for r in use]
+        reasons = sorted({n for r in use for n in r[1]})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": min(sm) if sm else None, "sm_max_mhz": mx, "reasons": reasons,
+                "samples": len(sm), "samples_inside_timed_regions": len(ins), "samples_total": len(rows), "source": source}
 
 
 def load_oracle(vst):
@@ -238,6 +326,13 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = vst.load_library()          # the CUDA library is mandatory; raises if missing
+    try:
+        uuid = str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local, uuid)   # started now (the poller needs ~1 s to come up), read after the e2e region
+    if rank == 0:
+        sampler.start()
 
     def barrier():
         torch.cuda.synchronize()
@@ -326,6 +421,7 @@ def main():
             fn()
         barrier()
         tot = 0.0
+        sampler.mark(True)
         for _ in range(steps):
             flush_buf.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -336,12 +432,10 @@ def main():
             e1.record()
             e1.synchronize()
             tot += e0.elapsed_time(e1)
+        sampler.mark(False)
         barrier()
         return max_over_ranks(tot / steps)
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     ms = timed(lambda: search_step(chosen), args.steps, args.warmup)
     ms_parity = timed(lambda: search_step(EF_PARITY), max(2, args.steps // 2), 1)
     # the search kernel alone (no collective) for the roofline
@@ -373,11 +467,22 @@ def main():
     for _ in range(max(1, args.warmup)):
         e2e_step()
     barrier()
+    sampler.mark(True)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    sampler.mark(False)
+    if world == 1 and rank == 0 and sampler.need_tail():
+        # the sampler was too slow for the millisecond-scale regions above (nvidia-smi fallback): keep the timed
+        # step itself running (not timed again) until it has seen the clocks under the same load
+        sampler.mark(True)
+        t_end = time.perf_counter() + 3.0
+        while sampler.need_tail() and time.perf_counter() < t_end:
+            search_step(chosen)
+            torch.cuda.synchronize()
+        sampler.mark(False)
     clocks = sampler.stop() if rank == 0 else None
     e2e_recall = recall(kh.numpy().view(np.uint64), truth)
 

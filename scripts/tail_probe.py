@@ -38,4 +38,5 @@ for mb in (32768,):
     print(f"max_batch {mb}: degree mean {deg.mean():.2f} full rows {np.mean(deg == 32):.3f} | evals mean {evs.mean():.1f} {pc(evs)} | expansions mean {exs.mean():.1f} {pc(exs)}", flush=True)
     dent, dres = np.array(dent), np.array(dres)
     print('corr(evals, entry dist)', np.corrcoef(evs, dent)[0,1], 'corr(evals, entry/top1)', np.corrcoef(evs, dent/np.maximum(dres,1e-9))[0,1], 'corr(evals, top1 dist)', np.corrcoef(evs, dres)[0,1], 'corr(exps, top1)', np.corrcoef(exs, dres)[0,1])
+    np.savez('gpurun_out/tail.npz', evs=evs, exs=exs, dent=dent, dres=dres)
     g.close()
