@@ -87,6 +87,7 @@ typedef struct vs_stats {
     uint64_t exact_tc_second_scan; /* ... of which needed a second tensor scan with a proven threshold */
     uint64_t exact_tc_scans;     /* exact-mode calls answered by the tensor-core path                  */
     double   exact_tc_scan_seconds; /* device time of their full scans (only while vs_set_stats is on)  */
+    uint64_t exact_stream_queries; /* exact-mode queries answered by the HBM-streaming scan (batches of <= 16 queries) */
 } vs_stats;
 
 /* usearch::Index::new + reserve — usearch.rs:82-99 (called from create_index, :38-53). */

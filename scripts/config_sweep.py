@@ -64,9 +64,13 @@ def main():
     p.add_argument("--reps", type=int, default=5)
     p.add_argument("--M", type=int, default=16)
     p.add_argument("--ef-add", type=int, default=128)
+    p.add_argument("--only-exact", action="store_true", help="brute-force legs only (use --M 2 --ef-add 8 for a cheap build)")
+    p.add_argument("--batches", default="", help="comma-separated query batch sizes overriding the config's")
     a = p.parse_args()
     c = dict(CONFIGS[a.config])
     n, nq, d, k = a.n or c["n"], a.nq or c["nq"], c["d"], c["k"]
+    if a.batches:
+        c["batches"] = [int(b) for b in a.batches.split(",")]
     metric = getattr(vst.Metric, c["metric"])
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
@@ -133,6 +137,7 @@ def main():
     sx = g.stats()
     out["exact"] = {"tc_queries": sx["exact_tc_queries"], "second_scan_queries": sx["exact_tc_second_scan"],
                     "fp32_fallback_queries": sx["exact_tc_fallback"], "by_batch": {}}
+    g.reset_stats()
     for b in sorted(set(c["batches"] + [nq])):
         if b > nq:
             continue
@@ -141,6 +146,12 @@ def main():
         out["exact"]["by_batch"][str(b)] = {"ms": ms, "qps": b / ms * 1e3, "tflops": fl / ms / 1e9, "frac_tf32_peak": fl / ms / 1e9 / tf32,
                                            "corpus_gbs": by / ms / 1e6, "frac_hbm_peak": by / ms / 1e6 / hbm}
         print(f"# exact B={b}: {ms:.3f} ms  {b / ms * 1e3:.0f} QPS  {fl / ms / 1e9:.0f} TFLOP/s  {by / ms / 1e6:.0f} GB/s", file=sys.stderr, flush=True)
+    out["exact"]["stream_queries"] = g.stats().get("exact_stream_queries", 0)
+    if a.only_exact:
+        out["peaks"] = {"hbm_gbs": hbm, "tf32_tflops": tf32}
+        g.close()
+        print(json.dumps(out), flush=True)
+        return
 
     # ANN: recall@k and QPS by ef on the whole query set, then by batch size at the smallest ef with recall >= 0.95
     out["ann"] = {"sweep": {}, "by_batch": {}}

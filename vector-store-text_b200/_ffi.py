@@ -34,7 +34,8 @@ class VsStats(C.Structure):
                 ("build_vectors", C.c_uint64), ("build_dist_evals", C.c_uint64), ("build_batches", C.c_uint64),
                 ("build_seconds", C.c_double), ("device_bytes", C.c_uint64), ("top_level", C.c_uint32),
                 ("dims", C.c_uint32), ("exact_tc_queries", C.c_uint64), ("exact_tc_fallback", C.c_uint64),
-                ("exact_tc_second_scan", C.c_uint64), ("exact_tc_scans", C.c_uint64), ("exact_tc_scan_seconds", C.c_double)]
+                ("exact_tc_second_scan", C.c_uint64), ("exact_tc_scans", C.c_uint64), ("exact_tc_scan_seconds", C.c_double),
+                ("exact_stream_queries", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

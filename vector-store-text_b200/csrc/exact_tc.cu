@@ -298,18 +298,27 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
 }
 
 
-// tau[q] = r-th smallest of the keys sampled for q over all slices (one warp per query).
-__global__ void k_tc_threshold(const float* __restrict__ samp, uint32_t slices, uint32_t nq, uint32_t nq_pad, uint32_t r, float* __restrict__ tau) {
-    const uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-    if (q >= nq) return;
+// tau[q] = r-th smallest of the keys sampled for q over all slices. One block per query: the samples are staged in
+// shared memory once, then r rounds of block-wide "smallest key after the previous pick" ((value, index) order, so
+// equal keys count separately). With a slice per CTA and several waves of CTAs there are thousands of samples per
+// query; the former one-warp-per-query form re-read them from global memory r times.
+constexpr int THR_THREADS = 128;
+__global__ void __launch_bounds__(THR_THREADS) k_tc_threshold(const float* __restrict__ samp, uint32_t slices, uint32_t nq, uint32_t nq_pad, uint32_t r,
+                                                             float* __restrict__ tau) {
+    extern __shared__ __align__(16) unsigned char thr_sm[];
+    float* v = reinterpret_cast<float*>(thr_sm);
+    __shared__ float wv[THR_THREADS / 32]; __shared__ uint32_t wi[THR_THREADS / 32];
+    const uint32_t q = blockIdx.x, t = threadIdx.x, lane = t & 31u, warp = t >> 5;
     const uint32_t total = slices * R_MAX;
+    for (uint32_t idx = t; idx < total; idx += THR_THREADS) v[idx] = samp[((size_t)(idx / R_MAX) * nq_pad + q) * R_MAX + (idx % R_MAX)];
+    __syncthreads();
     float pv = -INFINITY; uint32_t pi = 0; bool have = false;
     for (uint32_t round = 0; round < r; ++round) {
         float bv = INFINITY; uint32_t bi = NONE;
-        for (uint32_t idx = lane; idx < total; idx += 32) {
-            const float v = samp[((size_t)(idx / R_MAX) * nq_pad + q) * R_MAX + (idx % R_MAX)];
-            const bool after = !have || v > pv || (v == pv && idx > pi);
-            if (after && (v < bv || (v == bv && idx < bi))) { bv = v; bi = idx; }
+        for (uint32_t idx = t; idx < total; idx += THR_THREADS) {
+            const float x = v[idx];
+            const bool after = !have || x > pv || (x == pv && idx > pi);
+            if (after && (x < bv || (x == bv && idx < bi))) { bv = x; bi = idx; }
         }
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
@@ -317,10 +326,19 @@ __global__ void k_tc_threshold(const float* __restrict__ samp, uint32_t slices, 
             const uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (oi != NONE && (bi == NONE || ov < bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
         }
+        if (lane == 0) { wv[warp] = bv; wi[warp] = bi; }
+        __syncthreads();
+        bv = wv[0]; bi = wi[0];
+#pragma unroll
+        for (int w = 1; w < THR_THREADS / 32; ++w) {
+            const float ov = wv[w]; const uint32_t oi = wi[w];
+            if (oi != NONE && (bi == NONE || ov < bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+        }
+        __syncthreads();
         if (bi == NONE) { pv = INFINITY; break; }   // fewer than r samples: no usable threshold
         pv = bv; pi = bi; have = true;
     }
-    if (lane == 0) tau[q] = pv;
+    if (t == 0) tau[q] = pv;
 }
 
 __global__ void k_tc_max_norm(const float* __restrict__ sqn, uint32_t n, uint32_t* out_bits) {
@@ -496,7 +514,8 @@ static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm
     p.kblocks = (dpad + BK - 1) / BK;
     uint32_t want = (8u * (uint32_t)sm_count + p.nqt - 1) / p.nqt;          // ~8 waves of CTAs
     want = std::min<uint32_t>(want, std::max<uint32_t>(1u, p.n_tiles / 8));   // >= 8 tiles per CTA
-    want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 64u));
+    // (a cap of 64 slices left 64 of 148 SMs busy for a single query tile: 2.3 TB/s at 5M x 1536, B <= 128)
+    want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 1024u));
     p.tiles_per_slice = std::max<uint32_t>(1u, (p.n_tiles + want - 1) / want);
     p.slices = (p.n_tiles + p.tiles_per_slice - 1) / p.tiles_per_slice;
     // sampling stride: 32 on large corpora (the sample pass is the slow one per tile), denser on small ones so
@@ -583,7 +602,9 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     a.samp = S.samp; a.tau = S.tau; a.cand = S.cand; a.cnt = S.cnt; a.cap = p.cap;
     const dim3 grid(p.nqt, p.slices);
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
-    k_tc_threshold<<<(q.nq + 3) / 4, 128, 0, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, S.tau);
+    const size_t thr_smem = (size_t)p.slices * (EPI_WARPS / 4) * R_MAX * 4;
+    if (thr_smem > 48 * 1024) TC_TRY(cudaFuncSetAttribute(k_tc_threshold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)thr_smem));
+    k_tc_threshold<<<q.nq, THR_THREADS, thr_smem, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, S.tau);
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     const bool timing = stats && stats->time_scan && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess;
     if (timing) cudaEventRecord(ev0, st);

@@ -75,7 +75,7 @@ struct vs_index {
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0; size_t edge_cap = 0;
     // build scratch
-    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats; bool build_tc = true, zero_copy = true;
+    BuildBatch bb{}; uint32_t efpA = 128; DBuf<unsigned char> build_scratch, exact_scratch, tc_scratch, stage; TcStats tc_stats, tc_build_stats; bool build_tc = true, zero_copy = true; uint64_t st_stream_queries = 0;
     DBuf<uint32_t> tomb; DBuf<float> qpad, qdense, out_d; DBuf<uint64_t> out_k;
     unsigned long long* counters = nullptr; bool stats_on = false;
     // host state
@@ -330,7 +330,9 @@ vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t
         c.deleted = ix->deleted; c.slot_key = ix->slot_key; c.n_slots = ix->n_slots;
         ExactQueries q{}; q.q = ix->qpad.p; q.stride = ix->dpad; q.nq = (uint32_t)nq; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = 0; q.self_step = 0;
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
-        if (exact_tc_supported(c, q, (uint32_t)k)) {
+        const bool stream = exact_stream_supported(c, q, (uint32_t)k, ix->dev);   // K1s: HBM-streaming scan for <= 16 queries
+        if (stream) ix->st_stream_queries += nq;
+        if (!stream && exact_tc_supported(c, q, (uint32_t)k)) {
             // tcgen05 TF32 scan + exact FP32 re-rank (exact_tc.cu); same ids and distance bits as the FP32 kernel
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes((uint32_t)nq, c.n, (uint32_t)k, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
@@ -556,6 +558,7 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->top_level = (uint32_t)ix->top_level; o->dims = ix->dims;
     o->exact_tc_queries = ix->tc_stats.queries; o->exact_tc_fallback = ix->tc_stats.fp32_fallback; o->exact_tc_second_scan = ix->tc_stats.second_scan;
     o->exact_tc_scans = ix->tc_stats.scans; o->exact_tc_scan_seconds = ix->tc_stats.scan_ms * 1e-3;
+    o->exact_stream_queries = ix->st_stream_queries;
     return VS_OK;
 }
 vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; ix->tc_stats.time_scan = on != 0; return VS_OK; }
@@ -565,7 +568,7 @@ vs_status vs_reset_stats(vs_index* ix) {
     cudaSetDevice(ix->dev.device);
     CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
-    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; { const bool t = ix->tc_stats.time_scan; ix->tc_stats = TcStats(); ix->tc_stats.time_scan = t; }
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->st_stream_queries = 0; { const bool t = ix->tc_stats.time_scan; ix->tc_stats = TcStats(); ix->tc_stats.time_scan = t; }
     return VS_OK;
 }
 

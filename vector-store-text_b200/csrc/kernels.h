@@ -89,6 +89,9 @@ cudaError_t launch_exact(const ExactCorpus& c, const ExactQueries& q, int metric
                          uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
                          const ExactScratch& scratch, const DeviceInfo& dev, cudaStream_t st);
 
+// K1s (exact_kernels.cu): true when launch_exact answers this call with the HBM-streaming scan (few queries, contiguous corpus).
+bool exact_stream_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k, const DeviceInfo& dev);
+
 struct TcStats {                    // host-side counters of the tensor-core exact path
     uint64_t queries = 0, fp32_fallback = 0, second_scan = 0, scans = 0;
     double scan_ms = 0;             // device time of the full (emit) scans, measured with events when time_scan is set
