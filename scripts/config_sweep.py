@@ -141,11 +141,16 @@ def main():
     for b in sorted(set(c["batches"] + [nq])):
         if b > nq:
             continue
+        s0 = g.stats()
         ms = timed(b, exact=True)
+        s1 = g.stats()
         fl, by = 2.0 * b * n * d, n * d * 4.0
+        path = {kk: s1[kk] - s0[kk] for kk in ("exact_tc_queries", "exact_tc_second_scan", "exact_tc_fallback", "exact_stream_queries")}
         out["exact"]["by_batch"][str(b)] = {"ms": ms, "qps": b / ms * 1e3, "tflops": fl / ms / 1e9, "frac_tf32_peak": fl / ms / 1e9 / tf32,
-                                           "corpus_gbs": by / ms / 1e6, "frac_hbm_peak": by / ms / 1e6 / hbm}
-        print(f"# exact B={b}: {ms:.3f} ms  {b / ms * 1e3:.0f} QPS  {fl / ms / 1e9:.0f} TFLOP/s  {by / ms / 1e6:.0f} GB/s", file=sys.stderr, flush=True)
+                                           "corpus_gbs": by / ms / 1e6, "frac_hbm_peak": by / ms / 1e6 / hbm, "queries_by_path": path}
+        print(f"# exact B={b}: {ms:.3f} ms  {b / ms * 1e3:.0f} QPS  {fl / ms / 1e9:.0f} TFLOP/s  {by / ms / 1e6:.0f} GB/s   "
+              f"[stream {path['exact_stream_queries']} tc {path['exact_tc_queries']} 2nd-scan {path['exact_tc_second_scan']} fp32 {path['exact_tc_fallback']}]",
+              file=sys.stderr, flush=True)
     out["exact"]["stream_queries"] = g.stats().get("exact_stream_queries", 0)
     if a.only_exact:
         out["peaks"] = {"hbm_gbs": hbm, "tf32_tflops": tf32}

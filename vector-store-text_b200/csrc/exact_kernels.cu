@@ -281,6 +281,31 @@ k_exact_stream(const __grid_constant__ CUtensorMap cmap, ExactCorpus C, ExactQue
     };
     if (t == 0) for (uint32_t it = 0; it + 1 < nst && it < total; ++it) issue(it, it);
 
+    auto try_append = [&](const float (&dist)[NQ], unsigned& pend, uint32_t slot_id) {
+        if (!pend) return;
+#pragma unroll
+        for (int b = 0; b < NQ; ++b) if (pend >> b & 1u) {
+            if (dist[b] > thr[b]) { pend &= ~(1u << b); continue; }
+            const uint32_t pos = atomicAdd(&ccnt[b], 1u);
+            if (pos < SCB) { cbuf_d[b * SCB + pos] = dist[b]; cbuf_i[b * SCB + pos] = slot_id; pend &= ~(1u << b); }
+        }
+    };
+    auto merge_all = [&]() {   // warp b folds query b's buffer into its list; callers bracket it with block barriers
+        for (int b = warp; b < NQ; b += ST_THREADS / 32) {
+            const uint32_t cnt = min(ccnt[b], (uint32_t)SCB);
+            if (cnt == 0) continue;
+            SList L; const uint32_t w = par[b];
+            L.ld = lst_d + ((size_t)b * 2 + w) * kp; L.li = lst_i + ((size_t)b * 2 + w) * kp;
+            L.ld2 = lst_d + ((size_t)b * 2 + (w ^ 1u)) * kp; L.li2 = lst_i + ((size_t)b * 2 + (w ^ 1u)) * kp;
+            L.cap = (int)k; L.capp = (int)kp;
+            const float d = lane < (int)cnt ? cbuf_d[b * SCB + lane] : INFINITY;
+            const uint32_t id = lane < (int)cnt ? cbuf_i[b * SCB + lane] : NONE;
+            __syncwarp();
+            slist_merge(L, d, id, scr_id + warp * 32, scr_d + warp * 32, less);
+            __syncwarp();
+            if (lane == 0) { par[b] = w ^ 1u; thr[b] = L.ld[k - 1]; ccnt[b] = 0; }
+        }
+    };
     float2 acc[NP];
 #pragma unroll
     for (int b = 0; b < NP; ++b) acc[b] = make_float2(0.f, 0.f);
@@ -338,38 +363,21 @@ k_exact_stream(const __grid_constant__ CUtensorMap cmap, ExactCorpus C, ExactQue
                     for (int b = 0; b < NQ; ++b) if (slot_id == Q.self_first + (q0 + b) * Q.self_step) pend &= ~(1u << b);
                 }
             }
-            if (__syncthreads_or(pend != 0u)) {
-                for (;;) {
-                    if (pend) {
-#pragma unroll
-                        for (int b = 0; b < NQ; ++b) if (pend >> b & 1u) {
-                            if (dist[b] > thr[b]) { pend &= ~(1u << b); continue; }
-                            const uint32_t pos = atomicAdd(&ccnt[b], 1u);
-                            if (pos < SCB) { cbuf_d[b * SCB + pos] = dist[b]; cbuf_i[b * SCB + pos] = slot_id; pend &= ~(1u << b); }
-                        }
-                    }
-                    __syncthreads();
-                    for (int b = warp; b < NQ; b += ST_THREADS / 32) {
-                        const uint32_t cnt = min(ccnt[b], (uint32_t)SCB);
-                        if (cnt == 0) continue;
-                        SList L; const uint32_t w = par[b];
-                        L.ld = lst_d + ((size_t)b * 2 + w) * kp; L.li = lst_i + ((size_t)b * 2 + w) * kp;
-                        L.ld2 = lst_d + ((size_t)b * 2 + (w ^ 1u)) * kp; L.li2 = lst_i + ((size_t)b * 2 + (w ^ 1u)) * kp;
-                        L.cap = (int)k; L.capp = (int)kp;
-                        const float d = lane < (int)cnt ? cbuf_d[b * SCB + lane] : INFINITY;
-                        const uint32_t id = lane < (int)cnt ? cbuf_i[b * SCB + lane] : NONE;
-                        __syncwarp();
-                        slist_merge(L, d, id, scr_id + warp * 32, scr_d + warp * 32, less);
-                        __syncwarp();
-                        if (lane == 0) { par[b] = w ^ 1u; thr[b] = L.ld[k - 1]; ccnt[b] = 0; }
-                    }
-                    if (!__syncthreads_or(pend != 0u)) break;
-                }
+            // Lazy lists: candidates are only appended to the per-query buffers; the buffers are folded into the sorted
+            // lists (and the thresholds refreshed) when one overflows, so a block pays a merge round once per ~32
+            // accepted rows of a query instead of once per tile with any accepted row.
+            try_append(dist, pend, slot_id);
+            while (__syncthreads_or(pend != 0u)) {
+                merge_all();
+                __syncthreads();
+                try_append(dist, pend, slot_id);
             }
         }
         __syncthreads();   // every thread is done with this stage: thread 0 may refill it
         if (++slot == nst) { slot = 0; phase ^= 1u; }
     }
+    merge_all();   // what is still waiting in the buffers (the loop's last barrier made it visible)
+    __syncthreads();
     // the block's lists -> the per-(query, chunk) layout of k_exact_final (parity 0)
     for (uint32_t b = 0; b < nqv; ++b) {
         const size_t lb = (((size_t)(q0 + b) * P.nchunks + chunk) * 2) * kp;
@@ -425,14 +433,20 @@ static cudaError_t run_stream_metric(const CUtensorMap& cmap, const ExactCorpus&
     return cudaSuccess;
 }
 
-// One warp per query: fold the per-chunk lists into the final ascending top-k.
+// One warp per (query, group of chunks): fold the per-chunk lists into one ascending top-k.
+// groups == 1: the final answer goes to out_*; groups > 1 (first level of a two-level fold, streaming scan only,
+// whose lists all have parity 0): group g of query q leaves its list in the parity-1 buffer of chunk g.
+// in_par >= 0: every input list has that parity (second level), else par[] says which.
 template <class Less>
-__global__ void k_exact_final(ExactPlan P, uint32_t nq, uint32_t k, uint32_t out_ld, const float* part_d, const uint32_t* part_i, const uint8_t* par,
+__global__ void k_exact_final(ExactPlan P, uint32_t nq, uint32_t k, uint32_t out_ld, float* part_d, uint32_t* part_i, const uint8_t* par,
+                              uint32_t c_count, uint32_t groups, int in_par,
                               const uint64_t* __restrict__ slot_key, uint32_t* out_slots, uint64_t* out_keys, float* out_dist, Less less) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
-    const uint32_t q = blockIdx.x * wpb + warp;
-    if (q >= nq) return;
+    const uint32_t w = blockIdx.x * wpb + warp;
+    if (w >= nq * groups) return;
+    const uint32_t q = w / groups, grp = w - q * groups;
+    const uint32_t per = (c_count + groups - 1) / groups, c_begin = grp * per, c_end = min(c_count, c_begin + per);
     const uint32_t kp = P.kp;
     unsigned char* base = sm + (size_t)warp * (kp * 16 + 256);
     SList L;
@@ -440,13 +454,23 @@ __global__ void k_exact_final(ExactPlan P, uint32_t nq, uint32_t k, uint32_t out
     uint32_t* scr_id = L.li2 + kp; float* scr_d = (float*)(scr_id + 32);
     L.cap = (int)k; L.capp = (int)kp;
     slist_init(L);
-    for (uint32_t c = 0; c < P.nchunks; ++c) {
-        const size_t lb = (((size_t)q * P.nchunks + c) * 2 + par[(size_t)q * P.nchunks + c]) * kp;
+    for (uint32_t c = c_begin; c < c_end; ++c) {
+        const uint32_t pw = in_par >= 0 ? (uint32_t)in_par : par[(size_t)q * P.nchunks + c];
+        const size_t lb = (((size_t)q * P.nchunks + c) * 2 + pw) * kp;
         for (uint32_t b = 0; b < kp; b += 32) {
             const float d = part_d[lb + b + lane]; const uint32_t id = part_i[lb + b + lane];
             if (__ballot_sync(0xffffffffu, id != NONE) == 0u) break;
+            // chunk lists ascend: once the group's smallest entry cannot enter the full list, neither can the rest
+            const float d0 = __shfl_sync(0xffffffffu, d, 0); const uint32_t i0 = __shfl_sync(0xffffffffu, id, 0);
+            const float wd = L.ld[k - 1]; const uint32_t wi = L.li[k - 1];
+            if (wi != NONE && !less(d0, i0, wd, wi)) break;
             slist_merge(L, d, id, scr_id, scr_d, less);
         }
+    }
+    if (groups > 1) {
+        const size_t ob = (((size_t)q * P.nchunks + grp) * 2 + 1) * kp;
+        for (uint32_t i = lane; i < kp; i += 32) { part_d[ob + i] = i < k ? L.ld[i] : INFINITY; part_i[ob + i] = i < k ? L.li[i] : NONE; }
+        return;
     }
     for (uint32_t i = lane; i < out_ld; i += 32) {
         const uint32_t id = i < k ? L.li[i] : NONE;
@@ -471,8 +495,10 @@ static cudaError_t run_exact(const ExactCorpus& c, const ExactQueries& q, int me
     if (metric == COS) k_query_norms<<<(q.nq + 127) / 128, 128, 0, st>>>(q, qn);
     cudaError_t e = cudaSuccess;
     CUtensorMap cmap;
+    bool streamed = false;
     if (stream_applies(c, q, k, dev) && make_tmap_f32(&cmap, c.vecs, c.n, q.dpad, c.row_stride, SKC, SR, CU_TENSOR_MAP_SWIZZLE_128B)) {
         // K1s: HBM-bound streaming scan for a handful of queries; one block per SM, one chunk per block
+        streamed = true;
         const uint32_t tiles = (c.n + SR - 1) / SR, want = std::min<uint32_t>(tiles, (uint32_t)dev.sm_count);
         P.rows_per_chunk = ((tiles + want - 1) / want) * SR;
         P.nchunks = (c.n + P.rows_per_chunk - 1) / P.rows_per_chunk;
@@ -496,7 +522,20 @@ static cudaError_t run_exact(const ExactCorpus& c, const ExactQueries& q, int me
         e = cudaFuncSetAttribute(k_exact_final<Less>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    k_exact_final<Less><<<(q.nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(P, q.nq, k, out_ld, part_d, part_i, par, c.slot_key, out_slots, out_keys, out_dist, less);
+    // few queries after the streaming scan (one list per SM, all parity 0): fold in two levels so that the
+    // chain of dependent merges is ~2 sqrt(chunks) long instead of `chunks`
+    uint32_t groups = 1;
+    if (streamed && P.nchunks >= 32) { groups = 1; while (groups * groups < P.nchunks) ++groups; }
+    if (groups > 1) {
+        k_exact_final<Less><<<(q.nq * groups + wpb - 1) / wpb, wpb * 32, smem, st>>>(P, q.nq, k, out_ld, part_d, part_i, par, P.nchunks, groups, -1,
+                                                                                   c.slot_key, nullptr, nullptr, nullptr, less);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        k_exact_final<Less><<<(q.nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(P, q.nq, k, out_ld, part_d, part_i, par, groups, 1, 1,
+                                                                          c.slot_key, out_slots, out_keys, out_dist, less);
+        return cudaGetLastError();
+    }
+    k_exact_final<Less><<<(q.nq + wpb - 1) / wpb, wpb * 32, smem, st>>>(P, q.nq, k, out_ld, part_d, part_i, par, P.nchunks, 1, -1,
+                                                                      c.slot_key, out_slots, out_keys, out_dist, less);
     return cudaGetLastError();
 }
 

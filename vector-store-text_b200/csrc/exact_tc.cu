@@ -298,13 +298,26 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
 }
 
 
+// Worst-case |approximate distance - exact f32 distance| for one query (see the file header).
+__device__ __forceinline__ float tc_eps(int metric, float qn, float max_xn, uint32_t dpad) {
+    const float e_dot = 0.001953125f /* 2^-9: both operands truncated to TF32 */ + (float)dpad * 4.76837158e-7f /* d 2^-21: accumulation */;
+    const float e_f32 = (float)(dpad + 4) * 1.1920929e-7f;   // (d + 4) 2^-23: the two f32 chains
+    const float qx = sqrtf(qn) * sqrtf(max_xn);
+    float e;
+    if (metric == L2SQ) e = 2.f * qx * e_dot + (qn + max_xn) * e_f32 * 2.f;
+    else if (metric == IP) e = qx * (e_dot + e_f32);
+    else e = e_dot + e_f32 + 1e-6f;
+    return e * 1.25f;   // head-room for the rounding of this formula itself
+}
+
 // tau[q] = r-th smallest of the keys sampled for q over all slices. One block per query: the samples are staged in
 // shared memory once, then r rounds of block-wide "smallest key after the previous pick" ((value, index) order, so
 // equal keys count separately). With a slice per CTA and several waves of CTAs there are thousands of samples per
 // query; the former one-warp-per-query form re-read them from global memory r times.
 constexpr int THR_THREADS = 128;
 __global__ void __launch_bounds__(THR_THREADS) k_tc_threshold(const float* __restrict__ samp, uint32_t slices, uint32_t nq, uint32_t nq_pad, uint32_t r,
-                                                             float* __restrict__ tau) {
+                                                             uint32_t r0, float* __restrict__ tau, const float* __restrict__ qn,
+                                                             const uint32_t* __restrict__ max_xn_bits, int metric, uint32_t dpad, uint32_t stride, uint32_t cap, int widen) {
     extern __shared__ __align__(16) unsigned char thr_sm[];
     float* v = reinterpret_cast<float*>(thr_sm);
     __shared__ float wv[THR_THREADS / 32]; __shared__ uint32_t wi[THR_THREADS / 32];
@@ -312,7 +325,7 @@ __global__ void __launch_bounds__(THR_THREADS) k_tc_threshold(const float* __res
     const uint32_t total = slices * R_MAX;
     for (uint32_t idx = t; idx < total; idx += THR_THREADS) v[idx] = samp[((size_t)(idx / R_MAX) * nq_pad + q) * R_MAX + (idx % R_MAX)];
     __syncthreads();
-    float pv = -INFINITY; uint32_t pi = 0; bool have = false;
+    float pv = -INFINITY, p0 = -INFINITY; uint32_t pi = 0; bool have = false;
     for (uint32_t round = 0; round < r; ++round) {
         float bv = INFINITY; uint32_t bi = NONE;
         for (uint32_t idx = t; idx < total; idx += THR_THREADS) {
@@ -337,8 +350,29 @@ __global__ void __launch_bounds__(THR_THREADS) k_tc_threshold(const float* __res
         __syncthreads();
         if (bi == NONE) { pv = INFINITY; break; }   // fewer than r samples: no usable threshold
         pv = bv; pi = bi; have = true;
+        if (round + 1 == r0) p0 = pv;
     }
-    if (t == 0) tau[q] = pv;
+    // Widening. The proof in k_tc_select asks for d_k < dist(tau) - eps. p0, the sampled key of rank r0 ~ k / stride, estimates
+    // the k-th neighbour's key from above; when tau - p0 < 2 eps (dense neighbourhoods: 5M x 1536 clustered, k = 100 has
+    // hundreds of rows within eps of the k-th, two thirds of the queries failed the proof and paid a second full scan, 9.9 ms
+    // instead of 5.5 ms at B = 64) the threshold is raised by 2.5 eps: whenever k live rows have an approximate key <= the
+    // sampled tau, their exact distances are <= dist(tau) + eps < dist(tau + 2.5 eps) - eps and the proof holds. Not when the
+    // sample says the wider threshold would overflow the candidate buffer (12.5M x 96 L2: the bound is loose there, the
+    // unwidened proof succeeds for 99.9 % of the queries and widening made 5 % overflow).
+    float e = tc_eps(metric, qn[q], __uint_as_float(*max_xn_bits), dpad);
+    if (metric == COS) e *= sqrtf(qn[q]);          // dist = 1 + key / |q|
+    const float tw = pv + 2.5f * e;
+    uint32_t below = 0;
+    for (uint32_t idx = t; idx < total; idx += THR_THREADS) below += v[idx] <= tw ? 1u : 0u;
+    below = __reduce_add_sync(0xffffffffu, below);
+    if (lane == 0) wi[warp] = below;
+    __syncthreads();
+    if (t == 0) {
+        below = 0;
+        for (int w = 0; w < THR_THREADS / 32; ++w) below += wi[w];
+        const bool dense = (pv - p0) < 2.f * e, fits = (uint64_t)below * stride * 2u <= (uint64_t)cap;
+        tau[q] = (widen && dense && fits && isfinite(pv) && isfinite(tw)) ? tw : pv;
+    }
 }
 
 __global__ void k_tc_max_norm(const float* __restrict__ sqn, uint32_t n, uint32_t* out_bits) {
@@ -347,18 +381,6 @@ __global__ void k_tc_max_norm(const float* __restrict__ sqn, uint32_t n, uint32_
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));   // non-negative floats order like their bits
-}
-
-// Worst-case |approximate distance - exact f32 distance| for one query (see the file header).
-__device__ __forceinline__ float tc_eps(int metric, float qn, float max_xn, uint32_t dpad) {
-    const float e_dot = 0.001953125f /* 2^-9: both operands truncated to TF32 */ + (float)dpad * 4.76837158e-7f /* d 2^-21: accumulation */;
-    const float e_f32 = (float)(dpad + 4) * 1.1920929e-7f;   // (d + 4) 2^-23: the two f32 chains
-    const float qx = sqrtf(qn) * sqrtf(max_xn);
-    float e;
-    if (metric == L2SQ) e = 2.f * qx * e_dot + (qn + max_xn) * e_f32 * 2.f;
-    else if (metric == IP) e = qx * (e_dot + e_f32);
-    else e = e_dot + e_f32 + 1e-6f;
-    return e * 1.25f;   // head-room for the rounding of this formula itself
 }
 
 struct RerankArgs {
@@ -524,7 +546,7 @@ static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm
     p.stride = p.n_tiles >= 512 ? SAMPLE_STRIDE : std::min<uint32_t>(SAMPLE_STRIDE, std::max<uint32_t>(smin, p.n_tiles / 16));
     p.ok = sample_rank(k, p.stride) <= R_MAX && p.n_tiles >= 2 * p.stride;
     p.r = std::min<uint32_t>(R_MAX, sample_rank(k, p.stride));
-    uint32_t cap = 1; while (cap < 4u * p.r * p.stride) cap <<= 1;
+    uint32_t cap = 1; while (cap < (k >= 32 ? 8u : 4u) * p.r * p.stride) cap <<= 1;   // k >= 32: room for a widened threshold in dense data
     p.cap = cap;
     p.kp = (k + 31u) & ~31u;
     return p;
@@ -604,7 +626,11 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
     const size_t thr_smem = (size_t)p.slices * (EPI_WARPS / 4) * R_MAX * 4;
     if (thr_smem > 48 * 1024) TC_TRY(cudaFuncSetAttribute(k_tc_threshold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)thr_smem));
-    k_tc_threshold<<<q.nq, THR_THREADS, thr_smem, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, S.tau);
+    // sample rank whose key estimates the k-th neighbour's from above: ceil(k / stride) (rank 1 when the sample is sparser than k)
+    const uint32_t r0 = std::max<uint32_t>(1u, std::min<uint32_t>(p.r > 1 ? p.r - 1 : 1u, (kplan + p.stride - 1) / p.stride));
+    const char* we = getenv("VSANN_TC_WIDEN");   // 0 = sampled threshold as is (A/B switch)
+    k_tc_threshold<<<q.nq, THR_THREADS, thr_smem, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, r0, S.tau, S.qn, S.ctr + 1, metric, q.dpad,
+                                                        p.stride, p.cap, (!we || atoi(we) != 0) ? 1 : 0);
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     const bool timing = stats && stats->time_scan && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess;
     if (timing) cudaEventRecord(ev0, st);

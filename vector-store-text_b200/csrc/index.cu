@@ -330,9 +330,13 @@ vs_status search_device_locked(vs_index* ix, size_t nq, const float* d_q, size_t
         c.deleted = ix->deleted; c.slot_key = ix->slot_key; c.n_slots = ix->n_slots;
         ExactQueries q{}; q.q = ix->qpad.p; q.stride = ix->dpad; q.nq = (uint32_t)nq; q.dims = ix->dims; q.dpad = ix->dpad; q.self_first = 0; q.self_step = 0;
         ExactScratch sc{ix->exact_scratch.p, ix->exact_scratch.n};
-        const bool stream = exact_stream_supported(c, q, (uint32_t)k, ix->dev);   // K1s: HBM-streaming scan for <= 16 queries
+        // K1s, the HBM-streaming scan: always for <= 4 queries (measured on B200, 5M x 1536 / 12.5M x 96 / 1.25M x 768: 4.4 / 0.9 / 0.7 ms
+        // against 5.3 / 1.3 / 0.9 ms for the tensor path, whose fixed costs - sampling pass, re-rank, select - only pay off
+        // from ~8 queries), up to 16 queries when the tensor path does not apply (k > 128, small corpora)
+        const bool tc_ok = exact_tc_supported(c, q, (uint32_t)k);
+        const bool stream = exact_stream_supported(c, q, (uint32_t)k, ix->dev) && (nq <= 4 || !tc_ok);
         if (stream) ix->st_stream_queries += nq;
-        if (!stream && exact_tc_supported(c, q, (uint32_t)k)) {
+        if (!stream && tc_ok) {
             // tcgen05 TF32 scan + exact FP32 re-rank (exact_tc.cu); same ids and distance bits as the FP32 kernel
             CU(ix->tc_scratch.ensure(exact_tc_scratch_bytes((uint32_t)nq, c.n, (uint32_t)k, ix->dpad, ix->dev.sm_count)));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
