@@ -25,7 +25,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 D, K_NN, M, EF_ADD, EF_PARITY = 128, 10, 16, 128, 64
-EF_SWEEP = [16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1024]
+EF_SWEEP = [16, 18, 20, 22, 24, 28, 32, 40, 48, 56, 64, 96, 128, 192, 256, 384, 512, 768, 1024]   # the same grid for both arms
 
 
 def parse():
@@ -231,7 +231,7 @@ def cpu_pick_ef(vst, args, x, q):
     o.add_batch(np.arange(n, dtype=np.uint64), x[:n])
     truth, _, _ = o.search(q[:200], K_NN, exact=True)
     pick = EF_PARITY
-    for ef in (16, 24, 32, 48, 64):
+    for ef in [e for e in EF_SWEEP if e <= 64]:
         ak, _, _ = o.search(q[:200], K_NN, ef=ef)
         if recall(ak, truth) >= 0.95:
             pick = ef

@@ -88,6 +88,8 @@ typedef struct vs_stats {
     uint64_t exact_tc_scans;     /* exact-mode calls answered by the tensor-core path                  */
     double   exact_tc_scan_seconds; /* device time of their full scans (only while vs_set_stats is on)  */
     uint64_t exact_stream_queries; /* exact-mode queries answered by the HBM-streaming scan (batches of <= 16 queries) */
+    uint64_t search_host_queries;  /* queries that came through vs_search / vs_search_batch (host buffers) ...              */
+    uint64_t search_host_launches; /* ... and the launches that answered them: concurrent vs_search calls share a launch      */
 } vs_stats;
 
 /* usearch::Index::new + reserve — usearch.rs:82-99 (called from create_index, :38-53). */
@@ -109,7 +111,9 @@ vs_status vs_remove(vs_index* index, uint64_t key);
 /* usearch::Index::search(&embedding, limit) -> Matches{keys, distances} — usearch.rs:276,288,298.
  * Results ascending by (distance, key); *found <= k (fewer if the index is smaller).
  * ef_override == 0 => expansion_search; exact != 0 => brute force over all live vectors.
- * keys_out / dist_out hold nq x k entries; unused tail entries are UINT64_MAX / +inf. */
+ * keys_out / dist_out hold nq x k entries; unused tail entries are UINT64_MAX / +inf.
+ * vs_search calls that arrive from several threads while a launch is in flight are coalesced into the next launch
+ * (the reference runs up to 2 x T of them at once on its rayon pool, usearch.rs:118-131,275-276). */
 vs_status vs_search(vs_index* index, const float* query, size_t k,
                     uint64_t* keys_out, float* dist_out, size_t* found);
 vs_status vs_search_batch(vs_index* index, size_t nq, const float* queries, size_t k,

@@ -35,7 +35,7 @@ class VsStats(C.Structure):
                 ("build_seconds", C.c_double), ("device_bytes", C.c_uint64), ("top_level", C.c_uint32),
                 ("dims", C.c_uint32), ("exact_tc_queries", C.c_uint64), ("exact_tc_fallback", C.c_uint64),
                 ("exact_tc_second_scan", C.c_uint64), ("exact_tc_scans", C.c_uint64), ("exact_tc_scan_seconds", C.c_double),
-                ("exact_stream_queries", C.c_uint64)]
+                ("exact_stream_queries", C.c_uint64), ("search_host_queries", C.c_uint64), ("search_host_launches", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -225,6 +225,17 @@ class VsIndex:
         if single:
             return keys[0, :found[0]], dist[0, :found[0]]
         return keys, dist, found
+
+    def search_one(self, query, k):
+        """vs_search: one query, the library's default ef; concurrent callers share launches (include/vsann.h)."""
+        q = _f32(query)
+        if q.shape != (self.dims,):
+            raise VsError(VS_ERR_DIMS, f"ann: wrong embedding dimensions: {q.size} != {self.dims}")
+        keys = np.empty(k, dtype=np.uint64)
+        dist = np.empty(k, dtype=np.float32)
+        found = C.c_size_t()
+        self._check(self._fn("search")(self._h, _ptr(q), k, _ptr(keys), _ptr(dist), C.byref(found)))
+        return keys[:found.value], dist[:found.value]
 
     def search_device(self, nq, q_ptr, k, keys_ptr, dist_ptr, ef=0, exact=False, stream=0):
         self._check(self._fn("search_batch_device")(self._h, int(nq), C.c_void_p(int(q_ptr)), int(k), int(ef), 1 if exact else 0,

@@ -8,6 +8,7 @@
 //   size / capacity/reserve usearch.rs:201-212,308-311 -> vs_count / vs_capacity / vs_reserve
 // There is no CPU path in this library: every operation that touches vectors runs on the GPU.
 #include <algorithm>
+#include <condition_variable>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -84,6 +85,11 @@ struct vs_index {
     std::vector<uint64_t> host_slot_key;
     uint64_t st_build_vectors = 0, st_build_batches = 0; double st_build_seconds = 0; size_t device_bytes = 0;
     bool build_trace = false; std::vector<cudaEvent_t> trace_ev;   // VSANN_BUILD_TRACE=1: four events per batch (start, search, batch-knn, link)
+    // vs_search coalescer: single-query calls that arrive while a launch is in flight ride the next launch together
+    struct SearchReq { const float* q; size_t k; uint64_t* keys; float* dist; size_t* found; vs_status st; std::string err; bool done; };
+    std::mutex co_mu; std::condition_variable co_cv; std::vector<SearchReq*> co_q; bool co_leader = false, coalesce = true;
+    float* co_pin_q = nullptr; uint64_t* co_pin_k = nullptr; float* co_pin_d = nullptr; size_t co_cap_q = 0, co_cap_o = 0;
+    uint64_t st_search_calls = 0, st_search_launches = 0;
 
     GraphView view(uint32_t visible, int top) const {
         GraphView g{};
@@ -392,6 +398,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_GATHER4")) ix->dev.gather4 = atoi(e) != 0;
     if (const char* e = getenv("VSANN_SELECT_SMEM")) ix->dev.select_smem = atoi(e) != 0;
     if (const char* e = getenv("VSANN_ZERO_COPY")) ix->zero_copy = atoi(e) != 0;   // 0: always stage host queries with a copy
+    if (const char* e = getenv("VSANN_COALESCE")) ix->coalesce = atoi(e) != 0;     // 0: every vs_search call is its own launch
     if (const char* e = getenv("VSANN_BUILD_OVERLAP")) ix->build_overlap = atoi(e) != 0;   // 0: batch neighbours after the graph search, same stream
     if (const char* e = getenv("VSANN_BUILD_TRACE")) ix->build_trace = atoi(e) != 0;   // per-phase build timing on stderr
     if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
@@ -427,6 +434,7 @@ void vs_index_destroy(vs_index* ix) {
     if (ix->fork_ev) cudaEventDestroy(ix->fork_ev); if (ix->join_ev) cudaEventDestroy(ix->join_ev);
     if (ix->side) { cudaStreamSynchronize(ix->side); cudaStreamDestroy(ix->side); }
     if (ix->stream) cudaStreamDestroy(ix->stream);
+    if (ix->co_pin_q) cudaFreeHost(ix->co_pin_q); if (ix->co_pin_k) cudaFreeHost(ix->co_pin_k); if (ix->co_pin_d) cudaFreeHost(ix->co_pin_d);
     cudaGetLastError();
     delete ix;
 }
@@ -517,6 +525,7 @@ vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, si
         CU(cudaMemcpyAsync(ix->qdense.p, qs, nq * ix->dims * 4, cudaMemcpyHostToDevice, ix->stream));
         d_q = ix->qdense.p;
     }
+    ix->st_search_launches++; ix->st_search_calls += nq;
     s = search_device_locked(ix, nq, d_q, k, ef, exact, ix->out_k.p, ix->out_d.p, ix->stream); if (s != VS_OK) return s;
     // (results: writing them straight into pinned host memory from the kernel was measured and is no faster than
     // this 12 k B per query copy, so the explicit copy stays)
@@ -527,8 +536,74 @@ vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, si
     return VS_OK;
 }
 
+// One launch for every request of the round (requests with a different k go in separate launches). The queries are packed
+// into a pinned staging buffer the traversal kernel reads in place; results come back through pinned buffers.
+static void co_run(vs_index* ix, std::vector<vs_index::SearchReq*>& batch) {
+    size_t done = 0;
+    while (done < batch.size()) {
+        const size_t k = batch[done]->k;
+        std::vector<vs_index::SearchReq*> grp;
+        for (size_t i = done; i < batch.size(); ++i) if (batch[i]->k == k && batch[i]->st == (vs_status)-1) grp.push_back(batch[i]);
+        const size_t n = grp.size(), d = ix->dims;
+        vs_status s = VS_OK;
+        if (n * d > ix->co_cap_q) {
+            if (ix->co_pin_q) cudaFreeHost(ix->co_pin_q);
+            ix->co_pin_q = nullptr; ix->co_cap_q = 0;
+            const size_t want = std::max<size_t>(n * d, 256 * d);
+            if (cudaHostAlloc((void**)&ix->co_pin_q, want * 4, cudaHostAllocDefault) == cudaSuccess) ix->co_cap_q = want;
+            else { cudaGetLastError(); s = fail(VS_ERR_NOMEM, "search: pinned staging allocation failed"); }
+        }
+        if (s == VS_OK && n * k > ix->co_cap_o) {
+            if (ix->co_pin_k) cudaFreeHost(ix->co_pin_k); if (ix->co_pin_d) cudaFreeHost(ix->co_pin_d);
+            ix->co_pin_k = nullptr; ix->co_pin_d = nullptr; ix->co_cap_o = 0;
+            const size_t want = std::max<size_t>(n * k, 256 * k);
+            if (cudaHostAlloc((void**)&ix->co_pin_k, want * 8, cudaHostAllocDefault) == cudaSuccess &&
+                cudaHostAlloc((void**)&ix->co_pin_d, want * 4, cudaHostAllocDefault) == cudaSuccess) ix->co_cap_o = want;
+            else { cudaGetLastError(); s = fail(VS_ERR_NOMEM, "search: pinned staging allocation failed"); }
+        }
+        if (s == VS_OK) {
+            for (size_t i = 0; i < n; ++i) std::memcpy(ix->co_pin_q + i * d, grp[i]->q, d * sizeof(float));
+            s = vs_search_batch(ix, n, ix->co_pin_q, k, 0, 0, ix->co_pin_k, ix->co_pin_d, nullptr);
+        }
+        for (size_t i = 0; i < n; ++i) {
+            vs_index::SearchReq* r = grp[i];
+            r->st = s;
+            if (s != VS_OK) { r->err = g_err; continue; }
+            std::memcpy(r->keys, ix->co_pin_k + i * k, k * 8); std::memcpy(r->dist, ix->co_pin_d + i * k, k * 4);
+            if (r->found) { size_t f = 0; while (f < k && r->keys[f] != UINT64_MAX) ++f; *r->found = f; }
+        }
+        while (done < batch.size() && batch[done]->st != (vs_status)-1) ++done;
+    }
+}
+
+// usearch.rs:276 is called from up to 2 x T tasks at once (usearch.rs:118-131), each with ONE query. A GPU launch per query
+// would serialise them at ~0.3 ms each, so concurrent callers are coalesced: the first caller to arrive becomes the leader
+// and launches at once (no added latency on an idle index); whoever arrives while that launch is in flight queues up, and
+// the next leader takes the whole queue in one launch. Batch size adapts to the load by itself, no timer involved.
 vs_status vs_search(vs_index* ix, const float* q, size_t k, uint64_t* keys_out, float* dist_out, size_t* found) {
-    return vs_search_batch(ix, 1, q, k, 0, 0, keys_out, dist_out, found);
+    if (!ix || !q || !keys_out || !dist_out) return fail(VS_ERR_INVALID, "search: null argument");
+    if (k == 0) return fail(VS_ERR_INVALID, "search: k == 0");
+    if (!ix->coalesce) return vs_search_batch(ix, 1, q, k, 0, 0, keys_out, dist_out, found);
+    vs_index::SearchReq r{q, k, keys_out, dist_out, found, (vs_status)-1, std::string(), false};
+    std::unique_lock<std::mutex> l(ix->co_mu);
+    ix->co_q.push_back(&r);
+    while (!r.done) {
+        if (!ix->co_leader) {
+            ix->co_leader = true;
+            std::vector<vs_index::SearchReq*> batch; batch.swap(ix->co_q);
+            l.unlock();
+            co_run(ix, batch);
+            l.lock();
+            for (vs_index::SearchReq* b : batch) b->done = true;
+            ix->co_leader = false;
+            ix->co_cv.notify_all();
+        } else {
+            ix->co_cv.wait(l);
+        }
+    }
+    l.unlock();
+    if (r.st != VS_OK) g_err = r.err;
+    return r.st;
 }
 
 size_t vs_count(vs_index* ix) {
@@ -562,7 +637,7 @@ vs_status vs_get_stats(vs_index* ix, vs_stats* o) {
     o->top_level = (uint32_t)ix->top_level; o->dims = ix->dims;
     o->exact_tc_queries = ix->tc_stats.queries; o->exact_tc_fallback = ix->tc_stats.fp32_fallback; o->exact_tc_second_scan = ix->tc_stats.second_scan;
     o->exact_tc_scans = ix->tc_stats.scans; o->exact_tc_scan_seconds = ix->tc_stats.scan_ms * 1e-3;
-    o->exact_stream_queries = ix->st_stream_queries;
+    o->exact_stream_queries = ix->st_stream_queries; o->search_host_queries = ix->st_search_calls; o->search_host_launches = ix->st_search_launches;
     return VS_OK;
 }
 vs_status vs_set_stats(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; std::lock_guard<std::mutex> g(ix->mu); ix->stats_on = on != 0; ix->tc_stats.time_scan = on != 0; return VS_OK; }
@@ -572,7 +647,7 @@ vs_status vs_reset_stats(vs_index* ix) {
     cudaSetDevice(ix->dev.device);
     CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
-    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->st_stream_queries = 0; { const bool t = ix->tc_stats.time_scan; ix->tc_stats = TcStats(); ix->tc_stats.time_scan = t; }
+    ix->st_build_vectors = ix->st_build_batches = 0; ix->st_build_seconds = 0; ix->st_stream_queries = 0; ix->st_search_calls = ix->st_search_launches = 0; { const bool t = ix->tc_stats.time_scan; ix->tc_stats = TcStats(); ix->tc_stats.time_scan = t; }
     return VS_OK;
 }
 
