@@ -145,23 +145,32 @@ def test_traversal_matches_oracle_on_same_graph(vst, oracle_lib):
         g.close()
 
 
-def test_traversal_matches_oracle_large_graph(vst, oracle_lib):
+@pytest.mark.parametrize("ef,d,k", [(256, 32, 10), (512, 32, 10), (1024, 32, 100), (512, 768, 100), (1024, 128, 10)])
+def test_traversal_matches_oracle_large_graph(vst, oracle_lib, ef, d, k):
     """Same check on a multi-level index: the GPU beam from the oracle-visible entry (slot 0)
-    with a wide ef must return what the oracle's beam returns on the exported level-0 table."""
-    n, d, nq, ef, k = 4000, 32, 100, 256, 10
+    with a wide ef must return what the oracle's beam returns on the exported level-0 table
+    (ef 512 / 1024: the 16- and 32-register list variants of the traversal kernel)."""
+    n, nq = 4000, 100
     x = make_data(n, d, 43, clustered=True); q = make_data(nq, d, 44, clustered=True)
     g = vst.VsIndex(d, metric=1, capacity_hint=n, connectivity=16)
     g.add_batch(np.arange(n, dtype=np.uint64), x)
     links, _ = g.export_level(0)
     gk, gd, _ = g.search(q, k, ef=ef)
-    same = 0
+    same = overlap = 0
     for i in range(nq):
         slots = np.zeros(k, np.uint32); dist = np.zeros(k, np.float32); found = C.c_size_t()
         oracle_lib.ovs_graph_search(1, d, n, x.ctypes.data_as(C.c_void_p), links.ctypes.data_as(C.c_void_p), links.shape[1], None, 0,
                                     q[i].ctypes.data_as(C.c_void_p), k, ef, slots.ctypes.data_as(C.c_void_p),
                                     dist.ctypes.data_as(C.c_void_p), C.byref(found), None, None)
         same += gk[i].tolist() == slots.tolist()
-    assert same >= 0.97 * nq, same     # different entry points (hierarchy vs slot 0) may differ on a few queries
+        overlap += len(set(gk[i].tolist()) & set(slots.tolist()))
+    # different entry points (hierarchy vs slot 0) may differ on a few queries; with k = 100 in 768 dimensions the two
+    # summation orders (8-lane partial sums vs the oracle's sequential chain) also swap near-ties, so lists are compared as sets
+    print(f"traversal vs oracle beam ef={ef} d={d} k={k}: identical lists {same}/{nq}, overlap {overlap}/{nq * k}")
+    if k <= 10:
+        assert same >= 0.97 * nq, (same, overlap)
+    else:
+        assert overlap >= 0.995 * nq * k, (same, overlap)
     g.close()
 
 

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
 // Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
 // float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, VSANN_T_MINB) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+__global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : 2)) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                      uint32_t ef, uint32_t hsize, uint32_t stage_rows,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                      unsigned long long* counters, uint32_t* work) {
@@ -624,14 +624,17 @@ static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev) {
 template <int NL, int CPL>
 static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
-    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev), wpb = 4;
+    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev);
+    uint32_t wpb = 4;
+    // wide lists (ef > 256: NL = 16 / 32 list registers per lane) with long rows: fewer warps per block so that hash + staging fit
+    while (NL > 8 && wpb > 1 && tsmem_bytes(g.dpad, hs, rows) * wpb > dev.smem_per_block) wpb >>= 1;
     const size_t smem = tsmem_bytes(g.dpad, hs, rows) * wpb;
     if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     uint32_t* work = nullptr;
     if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
-    const uint32_t blocks = std::min<uint32_t>((nq + wpb - 1) / wpb, (uint32_t)dev.sm_count * VSANN_T_MINB);
+    const uint32_t blocks = std::min<uint32_t>((nq + wpb - 1) / wpb, (uint32_t)dev.sm_count * (NL <= 8 ? VSANN_T_MINB : 8));
     CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
     k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work);
     return cudaGetLastError();
@@ -685,12 +688,16 @@ static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, u
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                           uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
     if (nq == 0) return cudaSuccess;
-    if (dev.stage_bytes && !dev.force_smem_list && ef <= 256) {
+    if (dev.stage_bytes && !dev.force_smem_list && ef <= 1024) {
         cudaError_t e;
         if (ef <= 32) e = launch_search_tc<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
         else if (ef <= 64) e = launch_search_tc<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
         else if (ef <= 128) e = launch_search_tc<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else e = launch_search_tc<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 256) e = launch_search_tc<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        // ef up to 1024 (configs[4]'s recall sweep): the register list still beats the shared-memory list kernel
+        // (5M x 1536, k = 100: ef = 512 took 67 ms per 4096 queries there against 17.6 ms at ef = 256)
+        else if (ef <= 512) e = launch_search_tc<16>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else e = launch_search_tc<32>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
         if (e != cudaErrorInvalidConfiguration) return e;   // rows too long for the staging area: register-gather kernels below
     }
     if (!dev.force_smem_list) {
