@@ -799,6 +799,22 @@ cudaError_t launch_tombstone(uint32_t* deleted, const uint32_t* d_slots, uint32_
     return cudaGetLastError();
 }
 
+// found[q] = number of leading real keys of query q's result row (rows are padded with UINT64_MAX). Counting on the host
+// cost 65 us per 10 000 x 10 results (a single-thread pass over 800 KB that had just arrived by DMA): a tenth of the step.
+__global__ void k_count_found(const uint64_t* __restrict__ keys, uint32_t nq, uint32_t k, uint32_t* __restrict__ found) {
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const uint64_t* r = keys + (size_t)q * k;
+    uint32_t f = k;
+    while (f > 0 && r[f - 1] == 0xFFFFFFFFFFFFFFFFull) --f;
+    found[q] = f;
+}
+cudaError_t launch_count_found(const uint64_t* keys, uint32_t nq, uint32_t k, uint32_t* found, cudaStream_t st) {
+    if (nq == 0) return cudaSuccess;
+    k_count_found<<<(nq + 255) / 256, 256, 0, st>>>(keys, nq, k, found);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* keys_in, const float* dist_in,
                               uint64_t* keys_out, float* dist_out, cudaStream_t st) {
     if (nq == 0 || k == 0) return cudaSuccess;

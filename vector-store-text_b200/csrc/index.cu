@@ -88,6 +88,7 @@ struct vs_index {
     // vs_search coalescer: single-query calls that arrive while a launch is in flight ride the next launch together
     struct SearchReq { const float* q; size_t k; uint64_t* keys; float* dist; size_t* found; vs_status st; std::string err; bool done; };
     std::mutex co_mu; std::condition_variable co_cv; std::vector<SearchReq*> co_q; bool co_leader = false, coalesce = true;
+    DBuf<uint32_t> found_d; uint32_t* found_pin = nullptr; size_t found_cap = 0;   // per-query result counts (vs_search_batch's `found`)
     float* co_pin_q = nullptr; uint64_t* co_pin_k = nullptr; float* co_pin_d = nullptr; size_t co_cap_q = 0, co_cap_o = 0;
     uint64_t st_search_calls = 0, st_search_launches = 0;
 
@@ -434,6 +435,7 @@ void vs_index_destroy(vs_index* ix) {
     if (ix->fork_ev) cudaEventDestroy(ix->fork_ev); if (ix->join_ev) cudaEventDestroy(ix->join_ev);
     if (ix->side) { cudaStreamSynchronize(ix->side); cudaStreamDestroy(ix->side); }
     if (ix->stream) cudaStreamDestroy(ix->stream);
+    if (ix->found_pin) cudaFreeHost(ix->found_pin); ix->found_d.release();
     if (ix->co_pin_q) cudaFreeHost(ix->co_pin_q); if (ix->co_pin_k) cudaFreeHost(ix->co_pin_k); if (ix->co_pin_d) cudaFreeHost(ix->co_pin_d);
     cudaGetLastError();
     delete ix;
@@ -531,8 +533,20 @@ vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, si
     // this 12 k B per query copy, so the explicit copy stays)
     CU(cudaMemcpyAsync(keys_out, ix->out_k.p, nq * k * 8, cudaMemcpyDeviceToHost, ix->stream));
     CU(cudaMemcpyAsync(dist_out, ix->out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, ix->stream));
+    if (found) {   // counted on the device, 4 bytes per query come back
+        CU(ix->found_d.ensure(nq));
+        if (nq > ix->found_cap) {
+            if (ix->found_pin) cudaFreeHost(ix->found_pin);
+            ix->found_pin = nullptr; ix->found_cap = 0;
+            const size_t want = std::max<size_t>(nq, 16384);
+            CU(cudaHostAlloc((void**)&ix->found_pin, want * 4, cudaHostAllocDefault));
+            ix->found_cap = want;
+        }
+        CU(launch_count_found(ix->out_k.p, (uint32_t)nq, (uint32_t)k, ix->found_d.p, ix->stream));
+        CU(cudaMemcpyAsync(ix->found_pin, ix->found_d.p, nq * 4, cudaMemcpyDeviceToHost, ix->stream));
+    }
     CU(cudaStreamSynchronize(ix->stream));
-    if (found) for (size_t i = 0; i < nq; ++i) { size_t f = 0; while (f < k && keys_out[i * k + f] != UINT64_MAX) ++f; found[i] = f; }
+    if (found) for (size_t i = 0; i < nq; ++i) found[i] = ix->found_pin[i];
     return VS_OK;
 }
 
