@@ -298,7 +298,7 @@ def run_reference(args):
             "config": {"workload": workload_name(args), "M": M, "ef_add": EF_ADD, "ef_search": ef, "k": K_NN},
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def shard_q_fn(world, nq):
@@ -310,8 +310,28 @@ def workload_name(args):
             f"{args.nq} queries k={K_NN}")
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout. Libraries print there too (NCCL's "NCCL version ..." banner goes to fd 1 at
+    init), so fd 1 is pointed at stderr for the duration of the run and the line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
     args = parse()
+    quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
     import torch
@@ -381,11 +401,50 @@ def main():
     md = torch.empty((nq, K_NN), dtype=torch.float32, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
 
+    # ---- exchange step at N > 1. Default: fused gather + merge over peer memory - every rank's result lists
+    # live in symmetric memory (mapped into every peer over NVLink / NVSwitch), one cross-rank barrier on the stream, then K6
+    # loads the peers' lists directly: no all-gather, no gathered copy. Two buffers alternate so that one barrier per step
+    # is enough (a rank that passed barrier i+1 knows every peer finished merge i). VSANN_P2P_MERGE=0, or symmetric memory
+    # failing to come up, selects NCCL all_gather + the dense merge kernel.
+    p2p = None
+    if world > 1 and os.environ.get("VSANN_P2P_MERGE", "1") != "0":
+        try:
+            import torch.distributed._symmetric_memory as symm
+            grp = dist.group.WORLD
+            try:
+                symm.enable_symm_mem_for_group(grp.group_name)
+            except Exception:
+                pass
+            koff = nq * K_NN * 8
+            bufs = [symm.empty(nq * K_NN * 12, dtype=torch.uint8, device=dev) for _ in range(2)]
+            hdls = [symm.rendezvous(b_, grp) for b_ in bufs]
+            kptr = [torch.tensor([int(p_) for p_ in h.buffer_ptrs], dtype=torch.int64, device=dev) for h in hdls]
+            dptr = [torch.tensor([int(p_) + koff for p_ in h.buffer_ptrs], dtype=torch.int64, device=dev) for h in hdls]
+            p2p = {"bufs": bufs, "hdls": hdls, "kptr": kptr, "dptr": dptr, "koff": koff, "turn": 0}
+            torch.cuda.synchronize()
+        except Exception as e:   # noqa: BLE001
+            print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]}); using NCCL all_gather", file=sys.stderr)
+            p2p = None
+    exchange = "p2p loads from symmetric memory + fused merge kernel" if p2p else ("nccl all_gather + merge kernel" if world > 1 else "none")
+
+    def merge_published(i):
+        """Every rank's lists are in buffer i of the symmetric pair: barrier, then the fused gather + merge."""
+        p2p["hdls"][i].barrier(channel=0)
+        vst.merge_topk_peers_device(local, world, nq, K_NN, p2p["kptr"][i].data_ptr(), p2p["dptr"][i].data_ptr(), mk.data_ptr(), md.data_ptr(),
+                                    stream=stream, lib=lib)
+
     def search_step(ef, exact=False):
-        """One pass of the query batch: shard search, then (N > 1) all-gather + merge kernel (K6)."""
-        g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
+        """One pass of the query batch: shard search, then (N > 1) the exchange + merge kernel (K6)."""
         if world == 1:
+            g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
             return ok
+        if p2p:
+            i = p2p["turn"]; p2p["turn"] ^= 1
+            base = p2p["bufs"][i].data_ptr()
+            g.search_device(nq, qd.data_ptr(), K_NN, base, base + p2p["koff"], ef=ef, exact=exact, stream=stream)
+            merge_published(i)
+            return mk
+        g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
         dist.all_gather_into_tensor(gk.view(-1), ok.view(-1))
         dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
         vst.merge_topk_device(local, world, nq, K_NN, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=lib)
@@ -458,9 +517,16 @@ def main():
         stt = fn_host(g._h, nq, C.c_void_p(qh.data_ptr()), K_NN, chosen, 0, C.c_void_p(kh.data_ptr()), C.c_void_p(dh.data_ptr()), fh.ctypes.data_as(C.c_void_p))
         assert stt == 0
         if world > 1:   # results come back to the host per shard; merge on device as the serving rank would
-            ok.copy_(kh, non_blocking=True); od.copy_(dh, non_blocking=True)
-            dist.all_gather_into_tensor(gk.view(-1), ok.view(-1)); dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
-            vst.merge_topk_device(local, world, nq, K_NN, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=lib)
+            if p2p:
+                i = p2p["turn"]; p2p["turn"] ^= 1
+                buf = p2p["bufs"][i]
+                buf[:p2p["koff"]].view(torch.int64).view(nq, K_NN).copy_(kh, non_blocking=True)
+                buf[p2p["koff"]:].view(torch.float32).view(nq, K_NN).copy_(dh, non_blocking=True)
+                merge_published(i)
+            else:
+                ok.copy_(kh, non_blocking=True); od.copy_(dh, non_blocking=True)
+                dist.all_gather_into_tensor(gk.view(-1), ok.view(-1)); dist.all_gather_into_tensor(gd.view(-1), od.view(-1))
+                vst.merge_topk_device(local, world, nq, K_NN, gk.data_ptr(), gd.data_ptr(), mk.data_ptr(), md.data_ptr(), stream=stream, lib=lib)
             kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
             torch.cuda.synchronize()
 
@@ -524,14 +590,14 @@ def main():
                        "recall_at_10": sweep.get(chosen), "recall_target_reached": reached, "ef_sweep_recall": sweep,
                        "l2": "corpus 512 MB + links 128 MB per shard exceed the 126 MB L2; a 256 MB buffer is rewritten between timed steps",
                        "value_definition": "queries x shards / s: every rank answers every query on its own 1M-vector shard (N=1: plain QPS)",
-                       "parallelism": f"shard-by-key x{world}" + (" + nccl all_gather + merge kernel" if world > 1 else "")},
+                       "parallelism": f"shard-by-key x{world}" + (f" + {exchange}" if world > 1 else "")},
             "global_qps": nq / (ms * 1e-3),
             "parity_point": {"ef_search": EF_PARITY, "recall_at_10": sweep.get(EF_PARITY), "qps": shard_q / (ms_parity * 1e-3)},
             "build": {"vectors_per_s": n * world / build_dev, "seconds_device": build_dev, "seconds_wall": build_wall,
                       "batches": st["build_batches"], "unit": "vectors/s"},
             "e2e": {"value": shard_q / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * D * 4, "d2h_bytes_per_step": nq * K_NN * 12,
                     "ms_per_step": e2e_ms, "recall_at_10": e2e_recall},
-            "gpu_launches": args.steps * (1 if world == 1 else 2),   # per step: k_search_t (+ k_merge_topk after the all-gather)
+            "gpu_launches": args.steps * (1 if world == 1 else 2),   # per step: k_search_t (+ the merge kernel after the exchange)
             "exact": exact,
             "roofline": {"bound": "hbm", "kernel": "k_search_t", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel_ms": ms_kernel,
@@ -539,7 +605,7 @@ def main():
                                          "source": "oracle beam (ovs_graph_search) on the GPU-built graph, 200-query sample"}},
             "cpu_baseline": cb, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     g.close()
     if world > 1:
         dist.destroy_process_group()

@@ -146,6 +146,14 @@ vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k,
                                const uint64_t* d_keys_in, const float* d_dist_in,
                                uint64_t* d_keys_out, float* d_dist_out, void* stream);
 
+/* Fused gather + merge over peer memory: part p's lists (nq x k, ascending) are read in place from d_part_keys[p] /
+ * d_part_dist[p] - device pointers that may address a PEER GPU's memory mapped over NVLink / NVSwitch (CUDA IPC,
+ * symmetric memory) - so the exchange needs no all-gather and no gathered copy. d_part_keys / d_part_dist are DEVICE
+ * arrays of `parts` pointers. The caller orders the call after every shard's search (a cross-rank barrier). */
+vs_status vs_merge_topk_peers_device(int device, size_t parts, size_t nq, size_t k,
+                                     const uint64_t* const* d_part_keys, const float* const* d_part_dist,
+                                     uint64_t* d_keys_out, float* d_dist_out, void* stream);
+
 /* Debug/verification: copy the level-`level` neighbour table to the host.
  * links_out holds n_rows x row_width u32 slot ids (UINT32_MAX = empty);
  * slot_keys_out (may be NULL) holds the u64 key of each of the `slots` slots.

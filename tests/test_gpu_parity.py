@@ -229,6 +229,31 @@ def test_merge_topk_device(vst):
         assert ok[i].cpu().numpy().view(np.uint64).tolist() == [p[1] for p in allp]
 
 
+@pytest.mark.parametrize("parts,nq,k", [(5, 77, 10), (8, 300, 100), (2, 33, 1), (40, 50, 256)])
+def test_merge_topk_peers_device(vst, parts, nq, k):
+    """The fused gather + merge reads every part through its own pointer (peer memory in the multi-GPU bench; separate
+    local allocations here): same answer as a host merge, staged (small) and in-place (40 x 256 entries per query) modes."""
+    import torch
+    rng = np.random.default_rng(parts * 1000 + k)
+    dist = np.sort(rng.random((parts, nq, k), dtype=np.float32), axis=2)
+    keys = rng.permutation(parts * nq * k).astype(np.uint64).reshape(parts, nq, k)
+    if k > 4:
+        dist[1, :, 3] = dist[0, :, 4]                                     # cross-part ties -> key order
+        dist = np.sort(dist, axis=2)
+    pk = [torch.from_numpy(keys[p].view(np.int64).copy()).cuda() for p in range(parts)]
+    pd = [torch.from_numpy(dist[p].copy()).cuda() for p in range(parts)]
+    kp = torch.tensor([t.data_ptr() for t in pk], dtype=torch.int64, device="cuda")
+    dp = torch.tensor([t.data_ptr() for t in pd], dtype=torch.int64, device="cuda")
+    ok = torch.empty((nq, k), dtype=torch.int64, device="cuda"); od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    vst.merge_topk_peers_device(0, parts, nq, k, kp.data_ptr(), dp.data_ptr(), ok.data_ptr(), od.data_ptr())
+    torch.cuda.synchronize()
+    okh, odh = ok.cpu().numpy().view(np.uint64), od.cpu().numpy()
+    for i in range(nq):
+        allp = sorted(zip(dist[:, i, :].ravel().tolist(), keys[:, i, :].ravel().tolist()))[:k]
+        assert odh[i].tolist() == [p[0] for p in allp]
+        assert okh[i].tolist() == [p[1] for p in allp]
+
+
 def test_device_resident_search_and_add(vst):
     import torch
     n, d, nq, k = 5000, 64, 256, 10

@@ -11,7 +11,7 @@ VS_OK, VS_ERR_INVALID, VS_ERR_DIMS, VS_NOT_FOUND, VS_ERR_CAPACITY, VS_ERR_CUDA, 
 ABI_SYMBOLS = [
     "vs_index_create", "vs_index_destroy", "vs_add", "vs_add_batch", "vs_add_batch_device", "vs_remove",
     "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_count", "vs_capacity", "vs_reserve",
-    "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_export_level",
+    "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_export_level",
     "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
 ]
 
@@ -93,6 +93,7 @@ def load_library(path: str = None, prefix: str = "vs_"):
             "add_batch_device": (C.c_int, [vp, C.c_size_t, u64p, vp]),
             "search_batch_device": (C.c_int, [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_int, vp, vp, vp]),
             "merge_topk_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
+            "merge_topk_peers_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "export_level": (C.c_int, [vp, C.c_uint32, vp, szp, szp, vp, szp]),
             "index_save": (C.c_int, [vp, C.c_char_p]),
             "index_load": (C.c_int, [C.c_char_p, C.POINTER(VsOptions), C.POINTER(vp)]),
@@ -282,5 +283,14 @@ def merge_topk_device(device, parts, nq, k, keys_in_ptr, dist_in_ptr, keys_out_p
     lib = lib or load_library()
     st = lib.vs_merge_topk_device(int(device), int(parts), int(nq), int(k), C.c_void_p(int(keys_in_ptr)), C.c_void_p(int(dist_in_ptr)),
                                   C.c_void_p(int(keys_out_ptr)), C.c_void_p(int(dist_out_ptr)), C.c_void_p(int(stream)) if stream else None)
+    if st != VS_OK:
+        raise VsError(st, lib.vs_last_error().decode())
+
+
+def merge_topk_peers_device(device, parts, nq, k, part_keys_ptr, part_dist_ptr, keys_out_ptr, dist_out_ptr, stream=0, lib=None):
+    """Fused gather + merge: part_keys_ptr / part_dist_ptr are DEVICE arrays of `parts` pointers (peer memory allowed)."""
+    lib = lib or load_library()
+    st = lib.vs_merge_topk_peers_device(int(device), int(parts), int(nq), int(k), C.c_void_p(int(part_keys_ptr)), C.c_void_p(int(part_dist_ptr)),
+                                        C.c_void_p(int(keys_out_ptr)), C.c_void_p(int(dist_out_ptr)), C.c_void_p(int(stream)) if stream else None)
     if st != VS_OK:
         raise VsError(st, lib.vs_last_error().decode())

@@ -568,6 +568,51 @@ __global__ void k_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint
     }
 }
 
+// Fused gather + merge: part p's lists are read where they are - part_keys[p] / part_dist[p] may point
+// into a PEER GPU's memory mapped over NVLink / NVSwitch (symmetric memory) - so the exchange step needs no all-gather and
+// no gathered copy in HBM. A dependent tournament over remote loads would pay the NVLink latency k times, so the warp first
+// pulls all parts x k candidates of its query into shared memory in one round of independent loads, then merges locally.
+// STAGED = false: lists too large for shared memory are read in place (same tournament as k_merge_topk).
+template <bool STAGED>
+__global__ void k_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* __restrict__ part_keys,
+                                  const float* const* __restrict__ part_dist, uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
+    extern __shared__ __align__(16) unsigned char msm[];
+    const uint32_t warp = threadIdx.x >> 5, q = blockIdx.x * (blockDim.x >> 5) + warp, lane = lane_id();
+    if (q >= nq) return;
+    const uint32_t tot = parts * k;
+    uint64_t* sk = reinterpret_cast<uint64_t*>(msm) + (size_t)warp * tot;
+    float* sd = reinterpret_cast<float*>(msm + (size_t)(blockDim.x >> 5) * tot * 8) + (size_t)warp * tot;
+    if (STAGED) {
+        for (uint32_t i = lane; i < tot; i += 32) {
+            const uint32_t p = i / k, j = i - p * k;
+            sk[i] = part_keys[p][(size_t)q * k + j]; sd[i] = part_dist[p][(size_t)q * k + j];
+        }
+        __syncwarp();
+    }
+    uint32_t head[4] = {0, 0, 0, 0};   // lane l owns the heads of parts l, l + 32, ...: up to 128 parts
+    for (uint32_t o = 0; o < k; ++o) {
+        float bd = INFINITY; uint64_t bk = 0xFFFFFFFFFFFFFFFFull; uint32_t bp = NONE;
+        for (uint32_t j = 0, p = lane; p < parts && j < 4; ++j, p += 32) {
+            if (head[j] < k) {
+                float d; uint64_t key;
+                if (STAGED) { d = sd[p * k + head[j]]; key = sk[p * k + head[j]]; }
+                else { d = part_dist[p][(size_t)q * k + head[j]]; key = part_keys[p][(size_t)q * k + head[j]]; }
+                if (d < bd || (d == bd && key < bk)) { bd = d; bk = key; bp = p; }
+            }
+        }
+        float wd = bd; uint64_t wk = bk; uint32_t wp = bp;
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, wd, s);
+            const uint64_t ok = __shfl_xor_sync(0xffffffffu, wk, s);
+            const uint32_t op = __shfl_xor_sync(0xffffffffu, wp, s);
+            if (od < wd || (od == wd && (ok < wk || (ok == wk && op < wp)))) { wd = od; wk = ok; wp = op; }
+        }
+        if (lane == 0) { keys_out[(size_t)q * k + o] = wk; dist_out[(size_t)q * k + o] = wd; }
+        if (wp != NONE && (wp & 31u) == lane) ++head[wp >> 5];
+    }
+}
+
 // ------------------------------------------------- launchers ----------------------------------
 static inline uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
 
@@ -821,6 +866,22 @@ cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uin
     if (parts > 128) return cudaErrorInvalidValue;
     const uint32_t threads = 128, qpb = threads / 32;
     k_merge_topk<<<(nq + qpb - 1) / qpb, threads, 0, st>>>(parts, nq, k, keys_in, dist_in, keys_out, dist_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
+                                   uint64_t* keys_out, float* dist_out, cudaStream_t st) {
+    if (nq == 0 || k == 0 || parts == 0) return cudaSuccess;
+    if (parts > 128) return cudaErrorInvalidValue;
+    const uint32_t threads = 128, qpb = threads / 32;
+    const size_t smem = (size_t)qpb * parts * k * 12;
+    if (smem <= 96 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_merge_topk_ptrs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_merge_topk_ptrs<true><<<(nq + qpb - 1) / qpb, threads, smem, st>>>(parts, nq, k, part_keys, part_dist, keys_out, dist_out);
+    } else {
+        k_merge_topk_ptrs<false><<<(nq + qpb - 1) / qpb, threads, 0, st>>>(parts, nq, k, part_keys, part_dist, keys_out, dist_out);
+    }
     return cudaGetLastError();
 }
 

@@ -674,6 +674,15 @@ vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k, co
     return VS_OK;
 }
 
+vs_status vs_merge_topk_peers_device(int device, size_t parts, size_t nq, size_t k, const uint64_t* const* d_part_keys, const float* const* d_part_dist,
+                                     uint64_t* d_keys_out, float* d_dist_out, void* stream) {
+    if (!d_part_keys || !d_part_dist || !d_keys_out || !d_dist_out) return fail(VS_ERR_INVALID, "merge: null argument");
+    CU(cudaSetDevice(device));
+    CU(launch_merge_topk_ptrs((uint32_t)parts, (uint32_t)nq, (uint32_t)k, d_part_keys, d_part_dist, d_keys_out, d_dist_out, (cudaStream_t)stream));
+    if (!stream) CU(cudaStreamSynchronize(nullptr));
+    return VS_OK;
+}
+
 vs_status vs_export_level(vs_index* ix, uint32_t level, uint32_t* links_out, size_t* n_rows, size_t* row_width, uint64_t* slot_keys_out, size_t* slots) {
     if (!ix || !n_rows || !row_width) return fail(VS_ERR_INVALID, "export: null argument");
     std::lock_guard<std::mutex> g(ix->mu);

@@ -113,6 +113,8 @@ cudaError_t launch_link(const GraphView& g, const BuildBatch& b, const LinkTable
                         unsigned long long* counters, cudaStream_t st);
 cudaError_t launch_row_prepare(const float* d_src, float* vecs, float* sqn, uint32_t first, uint32_t n, uint32_t dims, uint32_t dpad, cudaStream_t st);
 cudaError_t launch_tombstone(uint32_t* deleted, const uint32_t* d_slots, uint32_t n, cudaStream_t st);
+cudaError_t launch_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
+                                   uint64_t* keys_out, float* dist_out, cudaStream_t st);
 cudaError_t launch_count_found(const uint64_t* keys, uint32_t nq, uint32_t k, uint32_t* found, cudaStream_t st);
 cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* keys_in, const float* dist_in,
                               uint64_t* keys_out, float* dist_out, cudaStream_t st);
