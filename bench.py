@@ -409,29 +409,12 @@ def main():
     p2p = None
     if world > 1 and os.environ.get("VSANN_P2P_MERGE", "1") != "0":
         try:
-            import torch.distributed._symmetric_memory as symm
-            grp = dist.group.WORLD
-            try:
-                symm.enable_symm_mem_for_group(grp.group_name)
-            except Exception:
-                pass
-            koff = nq * K_NN * 8
-            bufs = [symm.empty(nq * K_NN * 12, dtype=torch.uint8, device=dev) for _ in range(2)]
-            hdls = [symm.rendezvous(b_, grp) for b_ in bufs]
-            kptr = [torch.tensor([int(p_) for p_ in h.buffer_ptrs], dtype=torch.int64, device=dev) for h in hdls]
-            dptr = [torch.tensor([int(p_) + koff for p_ in h.buffer_ptrs], dtype=torch.int64, device=dev) for h in hdls]
-            p2p = {"bufs": bufs, "hdls": hdls, "kptr": kptr, "dptr": dptr, "koff": koff, "turn": 0}
-            torch.cuda.synchronize()
+            from vector_store_text_b200.sharded import PeerExchange   # the package's exchange: symmetric memory + fused merge
+            p2p = PeerExchange(nq, K_NN, dev, lib=lib)
         except Exception as e:   # noqa: BLE001
             print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]}); using NCCL all_gather", file=sys.stderr)
             p2p = None
     exchange = "p2p loads from symmetric memory + fused merge kernel" if p2p else ("nccl all_gather + merge kernel" if world > 1 else "none")
-
-    def merge_published(i):
-        """Every rank's lists are in buffer i of the symmetric pair: barrier, then the fused gather + merge."""
-        p2p["hdls"][i].barrier(channel=0)
-        vst.merge_topk_peers_device(local, world, nq, K_NN, p2p["kptr"][i].data_ptr(), p2p["dptr"][i].data_ptr(), mk.data_ptr(), md.data_ptr(),
-                                    stream=stream, lib=lib)
 
     def search_step(ef, exact=False):
         """One pass of the query batch: shard search, then (N > 1) the exchange + merge kernel (K6)."""
@@ -439,10 +422,9 @@ def main():
             g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
             return ok
         if p2p:
-            i = p2p["turn"]; p2p["turn"] ^= 1
-            base = p2p["bufs"][i].data_ptr()
-            g.search_device(nq, qd.data_ptr(), K_NN, base, base + p2p["koff"], ef=ef, exact=exact, stream=stream)
-            merge_published(i)
+            i, kp, dp = p2p.next_buffer()
+            g.search_device(nq, qd.data_ptr(), K_NN, kp, dp, ef=ef, exact=exact, stream=stream)
+            p2p.merge(i, mk, md)
             return mk
         g.search_device(nq, qd.data_ptr(), K_NN, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
         dist.all_gather_into_tensor(gk.view(-1), ok.view(-1))
@@ -518,11 +500,10 @@ def main():
         assert stt == 0
         if world > 1:   # results come back to the host per shard; merge on device as the serving rank would
             if p2p:
-                i = p2p["turn"]; p2p["turn"] ^= 1
-                buf = p2p["bufs"][i]
-                buf[:p2p["koff"]].view(torch.int64).view(nq, K_NN).copy_(kh, non_blocking=True)
-                buf[p2p["koff"]:].view(torch.float32).view(nq, K_NN).copy_(dh, non_blocking=True)
-                merge_published(i)
+                i, _, _ = p2p.next_buffer()
+                vk, vd = p2p.views(i)
+                vk.copy_(kh, non_blocking=True); vd.copy_(dh, non_blocking=True)
+                p2p.merge(i, mk, md)
             else:
                 ok.copy_(kh, non_blocking=True); od.copy_(dh, non_blocking=True)
                 dist.all_gather_into_tensor(gk.view(-1), ok.view(-1)); dist.all_gather_into_tensor(gd.view(-1), od.view(-1))

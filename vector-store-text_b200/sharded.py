@@ -2,9 +2,12 @@
 
   shard(key) = key mod world_size           — a replaced key stays on its shard
   add / remove                              — routed to the owning rank, no collective
-  ann                                       — every rank searches its shard with the full ef, one
-                                              all_gather of (dist f32, key u64)[B x k] per rank, then a
-                                              G-way merge per query (K6, csrc k_merge_topk)
+  ann                                       — every rank searches its shard with the full ef, then the
+                                              exchange + G-way merge per query (K6). On GPUs the exchange
+                                              is fused into the merge kernel (`PeerExchange`: result lists
+                                              in symmetric memory, one stream barrier, K6 loads the peers'
+                                              lists over NVLink / NVSwitch); otherwise one all_gather of
+                                              (dist f32, key u64)[B x k] per rank and the dense merge
   count                                     — all_reduce(sum) of the shard counts
 
 The collective is `torch.distributed` (NCCL over NVLink on the GPU box; gloo in the CPU tests, where
@@ -14,7 +17,53 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from ._ffi import VsIndex, merge_topk_device
+from ._ffi import VsIndex, merge_topk_device, merge_topk_peers_device
+
+
+class PeerExchange:
+    """Fused gather + merge over peer memory for `nq` x `k` result lists per rank.
+
+    Every rank owns two buffers in symmetric memory (keys u64 [nq, k] then dists f32 [nq, k]) that are mapped into
+    every peer. A step writes its shard's lists into buffer `turn` (the traversal kernel does so directly), calls
+    `merge()`: one cross-rank barrier on the current stream, then csrc k_merge_topk_ptrs pulls all peers' lists of a query
+    into shared memory in one round of NVLink loads and merges them. The buffers alternate, so one barrier per step is
+    enough: a rank that has passed barrier i+1 knows that every peer has finished merge i. Raises if symmetric memory
+    cannot be set up (callers fall back to all_gather)."""
+
+    def __init__(self, nq, k, device, group=None, lib=None):
+        import torch.distributed._symmetric_memory as symm
+        group = group or dist.group.WORLD
+        try:
+            symm.enable_symm_mem_for_group(group.group_name)
+        except Exception:   # noqa: BLE001  (newer torch: enabled implicitly)
+            pass
+        self.nq, self.k, self.device, self.lib = nq, k, device, lib
+        self.world = dist.get_world_size(group)
+        self.koff = nq * k * 8
+        self.bufs = [symm.empty(nq * k * 12, dtype=torch.uint8, device=device) for _ in range(2)]
+        self.hdls = [symm.rendezvous(b, group) for b in self.bufs]
+        self.kptr = [torch.tensor([int(p) for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
+        self.dptr = [torch.tensor([int(p) + self.koff for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
+        self.turn = 0
+        torch.cuda.synchronize(device)
+
+    def next_buffer(self):
+        """(index, keys device pointer, dists device pointer) of the buffer this step publishes into."""
+        i = self.turn
+        self.turn ^= 1
+        base = self.bufs[i].data_ptr()
+        return i, base, base + self.koff
+
+    def views(self, i):
+        b = self.bufs[i]
+        return b[:self.koff].view(torch.int64).view(self.nq, self.k), b[self.koff:].view(torch.float32).view(self.nq, self.k)
+
+    def merge(self, i, mk, md):
+        stream = torch.cuda.current_stream().cuda_stream
+        self.hdls[i].barrier(channel=0)
+        merge_topk_peers_device(self.device.index, self.world, self.nq, self.k, self.kptr[i].data_ptr(), self.dptr[i].data_ptr(),
+                                mk.data_ptr(), md.data_ptr(), stream=stream, lib=self.lib)
+        return mk, md
 
 
 def shard_of(keys, world):
@@ -40,6 +89,7 @@ class ShardedIndex:
         self.local = VsIndex(dims, device=(device.index if self.cuda else 0), lib=lib, **opts)
         self.dims = dims
         self._lib = lib
+        self._px = {}
 
     # -- mutation: each rank is handed the full batch and keeps its own keys -----------------------
     def add_batch(self, keys, vecs):
@@ -77,10 +127,31 @@ class ShardedIndex:
         mk, md = merge_topk_host(gk, gd, k)
         return mk.numpy().view(np.uint64), md.numpy()
 
-    def ann_device(self, qd, ok, od, k, ef=0, exact=False, gk=None, gd=None, mk=None, md=None):
-        """Device-resident path on the current torch stream: shard search -> all_gather -> merge kernel."""
+    def peer_exchange(self, nq, k):
+        """The PeerExchange for this (nq, k) shape, or None when symmetric memory is unavailable (collective: every rank calls)."""
+        key = (nq, k)
+        if key not in self._px:
+            try:
+                self._px[key] = PeerExchange(nq, k, self.device, lib=self._lib)
+            except Exception:   # noqa: BLE001
+                self._px[key] = None
+        return self._px[key]
+
+    def ann_device(self, qd, ok, od, k, ef=0, exact=False, gk=None, gd=None, mk=None, md=None, exchange="auto"):
+        """Device-resident path on the current torch stream: shard search -> exchange -> merge kernel.
+        exchange: "auto" (peer memory when it comes up, else all_gather), "p2p", "all_gather"."""
         nq = qd.shape[0]
         stream = torch.cuda.current_stream().cuda_stream
+        if self.world > 1 and exchange != "all_gather":
+            px = self.peer_exchange(nq, k)
+            if px is None and exchange == "p2p":
+                raise RuntimeError("symmetric memory is not available")
+            if px is not None:
+                i, kp, dp = px.next_buffer()
+                self.local.search_device(nq, qd.data_ptr(), k, kp, dp, ef=ef, exact=exact, stream=stream)
+                mk = torch.empty_like(ok) if mk is None else mk
+                md = torch.empty_like(od) if md is None else md
+                return px.merge(i, mk, md)
         self.local.search_device(nq, qd.data_ptr(), k, ok.data_ptr(), od.data_ptr(), ef=ef, exact=exact, stream=stream)
         if self.world == 1:
             return ok, od
