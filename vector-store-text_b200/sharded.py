@@ -33,10 +33,6 @@ class PeerExchange:
     def __init__(self, nq, k, device, group=None, lib=None):
         import torch.distributed._symmetric_memory as symm
         group = group or dist.group.WORLD
-        try:
-            symm.enable_symm_mem_for_group(group.group_name)
-        except Exception:   # noqa: BLE001  (newer torch: enabled implicitly)
-            pass
         self.nq, self.k, self.device, self.lib = nq, k, device, lib
         self.world = dist.get_world_size(group)
         self.koff = nq * k * 8
