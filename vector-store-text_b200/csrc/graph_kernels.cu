@@ -174,6 +174,149 @@ __global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : 2)) k_search_t(
     }
 }
 
+// ------------------------------------------------- K3b: one BLOCK per query (small batches) ----
+// With a handful of queries a warp per query leaves the GPU idle and a query waits for one warp to stream its
+// neighbour rows (5M x 1536, ef = 128: ~10 MB through one warp's 24 KB staging area = 1.1 ms per query). Here a block
+// of W warps serves one query: warp 0 (the leader) owns the candidate list, the visited hash and the link rows exactly
+// as in k_search_t; the up to 32 unvisited neighbours of an expansion are split among ALL warps, each warp streams
+// its share through its own staging area (the same stage_dist32 code, so the same distance bits), and the leader
+// continues with the distances. Two block barriers per expansion. Same lists as k_search_t, query by query.
+struct BlkShared { int n; uint32_t id[32]; float d[32]; };
+
+template <int CPL>
+__device__ __forceinline__ float blk_dist32(const GraphView& g, WarpSmem& S, WarpStage& T, const QRegs<CPL>& Q, float qn, BlkShared* B,
+                                            uint32_t nb /* leader lanes: ids or NONE */, bool go /* leader: false = finished */, bool& finished,
+                                            uint32_t& evals) {
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id(), W = blockDim.x >> 5;
+    int pos = 0;
+    if (warp == 0) {
+        const unsigned valid = __ballot_sync(0xffffffffu, go && nb != NONE);
+        pos = __popc(valid & ((1u << lane) - 1u));
+        if (go && nb != NONE) B->id[pos] = nb;
+        if (lane == 0) B->n = go ? __popc(valid) : -1;
+    }
+    __syncthreads();
+    const int n = B->n;
+    finished = n < 0;
+    if (finished) return INFINITY;
+    const int R = 4 * ((n + 4 * (int)W - 1) / (4 * (int)W));            // ids per warp: whole gather4 groups
+    const int mine = (int)warp * R + (int)lane;
+    const uint32_t id = (R > 0 && (int)lane < R && mine < n) ? B->id[mine] : NONE;
+    uint32_t ev = 0;
+    const float d = stage_dist32<CPL>(g, S, T, Q, qn, id, ev);
+    if (id != NONE) B->d[mine] = d;
+    __syncthreads();
+    if (warp == 0) evals += (uint32_t)n;
+    return (warp == 0 && nb != NONE) ? B->d[pos] : INFINITY;
+}
+
+template <int NL, int CPL>
+__global__ void __launch_bounds__(256) k_search_blk(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries,
+                                                    uint32_t nq, uint32_t k, uint32_t ef, uint32_t hsize, uint32_t stage_rows,
+                                                    uint64_t* __restrict__ keys_out, float* __restrict__ dist_out, unsigned long long* counters) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ BlkShared B;
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
+    WarpSmem S; WarpStage T;
+    carve_tsmem(smem + warp * per_warp, g.dpad, hsize, stage_rows, S, T);
+    if (use_vmap) T.tmap = &vmap;
+    T.pf_over = true;
+    const uint32_t q = blockIdx.x;
+    if (q >= nq) return;
+    uint32_t evals = 0, exps = 0;
+    warp_load_query(S.q4, queries + (size_t)q * g.dims, g.dims, g.dpad);      // every warp keeps its own copy of the query
+    QRegs<CPL> Q; Q.load(S.q4);
+    uint64_t* ko = keys_out + (size_t)q * k; float* dd = dist_out + (size_t)q * k;
+    uint32_t nout = 0;
+    if (g.n_slots > 0) {
+        const float qn = g.metric == COS ? warp_sqnorm(S.q4, g.chunks) : 0.f;
+        bool fin;
+        // entry point, then the greedy descent (leader decides, everybody evaluates)
+        uint32_t cur = 0;
+        float dcur = blk_dist32<CPL>(g, S, T, Q, qn, &B, lane == 0 ? 0u : NONE, true, fin, evals);
+        dcur = __shfl_sync(0xffffffffu, dcur, 0);
+        for (int l = g.top_level; l >= 1; --l) {
+            for (;;) {
+                uint32_t nb = NONE;
+                if (warp == 0) {
+                    int width; const uint32_t* row = level_row(g, l, cur, width);
+                    ++exps;
+                    nb = ((int)lane < width) ? row[lane] : NONE;
+                    if (nb != NONE && nb >= g.n_slots) nb = NONE;
+                }
+                const float d = blk_dist32<CPL>(g, S, T, Q, qn, &B, nb, true, fin, evals);
+                int moved = 0;
+                if (warp == 0) {
+                    float bd = nb != NONE ? d : INFINITY; uint32_t bi = nb;
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) {
+                        const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+                        const uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                        if (pair_less(od, oi, bd, bi)) { bd = od; bi = oi; }
+                    }
+                    if (bi != NONE && bd < dcur) { cur = bi; dcur = bd; moved = 1; }
+                    if (lane == 0) B.n = moved;     // published by the next barrier below
+                }
+                __syncthreads();
+                moved = B.n;
+                __syncthreads();
+                if (!moved) break;
+            }
+        }
+        RList<NL> L;
+        if (warp == 0) rbeam_seed(S, L, (int)ef, cur, dcur);
+        for (;;) {
+            uint32_t nb = NONE; bool go = false;
+            if (warp == 0) {
+                float dc; const uint32_t c = L.pop(dc);
+                go = c != NONE;
+                if (go) {
+                    ++exps;
+                    int width; const uint32_t* row = level_row(g, 0, c, width);
+                    nb = ((int)lane < width) ? row[lane] : NONE;
+                    if (nb != NONE && nb >= g.n_slots) nb = NONE;
+                    if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+                    __syncwarp();
+                }
+            }
+            const float d = blk_dist32<CPL>(g, S, T, Q, qn, &B, nb, go, fin, evals);
+            if (fin) break;
+            if (warp == 0) {
+                const bool good = nb != NONE && d < L.worst;
+                if (good) { int w2; prefetch_l2(level_row(g, 0, nb, w2)); }
+                unsigned acc = __ballot_sync(0xffffffffu, good);
+                while (acc) {
+                    const int src = __ffs(acc) - 1; acc &= acc - 1;
+                    const float nd = __shfl_sync(0xffffffffu, d, src);
+                    const uint32_t nid = __shfl_sync(0xffffffffu, nb, src);
+                    if (nd < L.worst) L.insert(nd, nid);
+                }
+            }
+        }
+        if (warp == 0) {
+#pragma unroll
+            for (int j = 0; j < NL; ++j) {
+                const uint32_t id = L.id[j] & ~EXPANDED;
+                const bool live = L.id[j] != NONE && !is_deleted(g, id);
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
+                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
+                nout += __popc(m);
+            }
+            if (nout > k) nout = k;
+        }
+    }
+    if (warp == 0) {
+        for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
+        if (counters && lane == 0) {
+            atomicAdd(&counters[0], 1ull);
+            atomicAdd(&counters[1], (unsigned long long)evals);
+            atomicAdd(&counters[2], (unsigned long long)exps);
+        }
+    }
+}
+
 // ------------------------------------------------- K4a: insertion search on the frozen graph --
 // One warp per batch item: greedy descent from the top, then an ef_add beam on every level the
 // item lives on; each level's sorted candidate list goes to scratch (cand_id / cand_d).
@@ -730,9 +873,42 @@ static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, u
     return cudaGetLastError();
 }
 
+template <int NL, int CPL>
+static cudaError_t launch_search_blk_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev);
+    const size_t per_warp = tsmem_bytes(g.dpad, hs, rows);
+    uint32_t W = 8;
+    while (W > 1 && per_warp * W + 1024 > dev.smem_per_block) --W;
+    if (W < 2) return cudaErrorInvalidConfiguration;
+    const size_t smem = per_warp * W;
+    cudaError_t e = cudaFuncSetAttribute(k_search_blk<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
+    k_search_blk<NL, CPL><<<nq, W * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters);
+    return cudaGetLastError();
+}
+template <int NL>
+static cudaError_t launch_search_blk_c(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
+                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+    if (g.chunks == 32) return launch_search_blk_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+    return launch_search_blk_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+}
+
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                           uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
     if (nq == 0) return cudaSuccess;
+    // small batches: a block per query (K3b) - the SMs would idle otherwise and each query is latency bound on one warp
+    static const uint32_t blk_max = [] { const char* e = getenv("VSANN_BLOCK_QUERY_MAX"); return e ? (uint32_t)atoi(e) : 0xFFFFFFFFu; }();
+    const uint32_t blk_limit = blk_max != 0xFFFFFFFFu ? blk_max : 2u * (uint32_t)dev.sm_count;
+    if (dev.stage_bytes && !dev.force_smem_list && ef <= 256 && nq <= blk_limit) {
+        cudaError_t e;
+        if (ef <= 32) e = launch_search_blk_c<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 64) e = launch_search_blk_c<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 128) e = launch_search_blk_c<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else e = launch_search_blk_c<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (e != cudaErrorInvalidConfiguration) return e;
+    }
     if (dev.stage_bytes && !dev.force_smem_list && ef <= 1024) {
         cudaError_t e;
         if (ef <= 32) e = launch_search_tc<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
