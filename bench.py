@@ -67,6 +67,13 @@ def recall(found, truth):
 _POLLER = r"""
 import os, subprocess, sys, time
 gpu, uuid, out = int(sys.argv[1]), sys.argv[2], open(sys.argv[3], "w", buffering=1)
+try:   # stay out of the timed process's way: lowest priority, last core
+    os.nice(19)
+    cpus = sorted(os.sched_getaffinity(0))
+    if len(cpus) > 2:
+        os.sched_setaffinity(0, {cpus[-1]})
+except Exception:
+    pass
 Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 try:
     import pynvml as nv
@@ -92,7 +99,7 @@ try:
         except Exception:
             b = 0
         out.write("%.6f,%d,%d,%d,%d,%d\n" % ((time.time(), mhz) + tuple(1 if b & m else 0 for m in masks)))
-        time.sleep(0.001)
+        time.sleep(0.002)
 except Exception as e:
     out.write("# nvidia-smi (nvml failed: %s)\n" % (str(e)[:80],))
     p = subprocess.Popen(["nvidia-smi", "-i", str(gpu), "--query-gpu=" + Q, "--format=csv,noheader,nounits", "-lms", "20"],
@@ -107,7 +114,7 @@ except Exception as e:
 class ClockSampler:
     """SM clocks + throttle reasons under load (B200_PROFILING.md clocks line). The timed regions are a few
     milliseconds long, shorter than one `nvidia-smi -lms` period, so a separate process (no GIL shared with the
-    timed loop) polls NVML every millisecond and timestamps each sample; `mark(True/False)` records the wall-clock
+    timed loop) polls NVML every 2 ms (niced, pinned to the last core) and timestamps each sample; `mark(True/False)` records the wall-clock
     windows of the timed regions and the medians are taken over the samples that fell inside them. When NVML cannot
     be loaded the poller falls back to `nvidia-smi -lms 20`, and bench.py keeps the timed step itself running until
     a few samples have arrived (`need_tail`)."""
@@ -514,6 +521,8 @@ def main():
     for _ in range(max(1, args.warmup)):
         e2e_step()
     barrier()
+    import gc
+    gc.collect(); gc.disable()          # a collection inside a 6 ms region would be a tenth of it
     sampler.mark(True)
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -521,6 +530,7 @@ def main():
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
     sampler.mark(False)
+    gc.enable()
     if world == 1 and rank == 0 and sampler.need_tail():
         # the sampler was too slow for the millisecond-scale regions above (nvidia-smi fallback): keep the timed
         # step itself running (not timed again) until it has seen the clocks under the same load

@@ -30,6 +30,23 @@ def build_actor(force: bool = False) -> str:
     return ACTOR_OUT
 
 
+LOAD_OUT = os.path.join(HERE, "lib", "actor_load")
+LOAD_SRC = os.path.join(CSRC, "actor_load.cpp")
+
+
+def build_actor_load(force: bool = False) -> str:
+    """lib/actor_load: native load generator for the actor (links libvsactor.so, dlopen-s the backend)."""
+    deps = [LOAD_SRC, ACTOR_OUT] + ACTOR_DEPS
+    if not force and os.path.exists(LOAD_OUT) and all(os.path.getmtime(d) <= os.path.getmtime(LOAD_OUT) for d in deps):
+        return LOAD_OUT
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-pthread", "-o", LOAD_OUT, LOAD_SRC,
+           "-L" + os.path.dirname(ACTOR_OUT), "-lvsactor", "-ldl", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return LOAD_OUT
+
+
 def needs_build() -> bool:
     if not os.path.exists(OUT):
         return True
@@ -40,6 +57,7 @@ def needs_build() -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> str:
     build_actor(force)
+    build_actor_load(force)
     if not force and not needs_build():
         return OUT
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
