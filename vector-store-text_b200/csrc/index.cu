@@ -84,6 +84,8 @@ struct vs_index {
     std::vector<uint64_t> pend_keys; std::vector<float> pend_vecs; std::unordered_map<uint64_t, size_t> pend_pos;
     std::vector<uint64_t> host_slot_key;
     uint64_t st_build_vectors = 0, st_build_batches = 0; double st_build_seconds = 0; size_t device_bytes = 0;
+    static constexpr int KNN_SETS = 3;   // neighbour buffers: batch i links from one while the side stream fills the next two
+    uint32_t* knn_set_id[KNN_SETS][MAX_LEVELS] = {}; float* knn_set_d[KNN_SETS][MAX_LEVELS] = {}; cudaEvent_t knn_done[KNN_SETS] = {}, link_done[KNN_SETS] = {}; int build_pipeline = 1;   // batches of look-ahead for the intra-batch neighbours (2 measured equal to 1)
     bool build_trace = false; std::vector<cudaEvent_t> trace_ev;   // VSANN_BUILD_TRACE=1: four events per batch (start, search, batch-knn, link)
     // vs_search coalescer: single-query calls that arrive while a launch is in flight ride the next launch together
     struct SearchReq { const float* q; size_t k; uint64_t* keys; float* dist; size_t* found; vs_status st; std::string err; bool done; };
@@ -164,13 +166,14 @@ vs_status do_reserve(vs_index* ix, size_t cap) {
 vs_status setup_build_scratch(vs_index* ix) {
     const uint32_t B = ix->max_batch, efp = build_efp(ix->efA), kbp = KNN_BATCH;
     ix->efpA = efp;
-    size_t bytes = 0; size_t off_ci[MAX_LEVELS], off_cd[MAX_LEVELS], off_cn[MAX_LEVELS], off_ki[MAX_LEVELS], off_kd[MAX_LEVELS];
+    size_t bytes = 0; size_t off_ci[MAX_LEVELS], off_cd[MAX_LEVELS], off_cn[MAX_LEVELS], off_ki[MAX_LEVELS], off_kd[MAX_LEVELS], off_kis[2][MAX_LEVELS], off_kds[2][MAX_LEVELS];
     auto take = [&](size_t b) { size_t o = bytes; bytes += (b + 255) & ~(size_t)255; return o; };
     size_t items_total = 0; uint64_t s = 1;
     for (int l = 0; l < MAX_LEVELS; ++l) {
         const size_t it = B / s + 2; items_total += it;
         off_ci[l] = take(it * efp * 4); off_cd[l] = take(it * efp * 4); off_cn[l] = take(it * 4);
         off_ki[l] = take(it * kbp * 4); off_kd[l] = take(it * kbp * 4);
+        for (int e = 0; e < 2; ++e) { off_kis[e][l] = take(it * kbp * 4); off_kds[e][l] = take(it * kbp * 4); }   // further sets: the neighbours of batches i+1, i+2 are computed while batch i searches and links
         s *= ix->M; if (s > 0xFFFFFFFFull) s = 0xFFFFFFFFull;
     }
     ix->edge_cap = items_total * ix->M;
@@ -183,6 +186,8 @@ vs_status setup_build_scratch(vs_index* ix) {
     for (int l = 0; l < MAX_LEVELS; ++l) {
         ix->bb.cand_id[l] = (uint32_t*)(p + off_ci[l]); ix->bb.cand_d[l] = (float*)(p + off_cd[l]); ix->bb.cand_n[l] = (uint32_t*)(p + off_cn[l]);
         ix->bb.knn_id[l] = (uint32_t*)(p + off_ki[l]); ix->bb.knn_d[l] = (float*)(p + off_kd[l]);
+        ix->knn_set_id[0][l] = ix->bb.knn_id[l]; ix->knn_set_d[0][l] = ix->bb.knn_d[l];
+        for (int e = 0; e < 2; ++e) { ix->knn_set_id[e + 1][l] = (uint32_t*)(p + off_kis[e][l]); ix->knn_set_d[e + 1][l] = (float*)(p + off_kds[e][l]); }
     }
     ix->lt.n_edges = (uint32_t*)(p + o_ne); ix->lt.n_touched = ix->lt.n_edges + 1;
     ix->lt.edge_row = (uint32_t*)(p + o_er); ix->lt.edge_src = (uint32_t*)(p + o_es);
@@ -194,14 +199,12 @@ vs_status setup_build_scratch(vs_index* ix) {
 
 // K4 + K5 for slots [first, first + count): search on the frozen graph, intra-batch exact
 // neighbours, heuristic selection, reverse-link merge.
-vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
-    BuildBatch b = ix->bb;   // scratch pointers
+// Levels and item ranges of the batch [first, first + count).
+static void batch_shape(vs_index* ix, uint32_t first, uint32_t count, BuildBatch& b) {
     b.first_slot = first; b.count = count;
     b.new_top = top_for(ix, first + count);
     uint32_t off = 0;
-    uint32_t* knn_id_saved[MAX_LEVELS]; float* knn_d_saved[MAX_LEVELS];
     for (int l = 0; l < MAX_LEVELS; ++l) {
-        knn_id_saved[l] = b.knn_id[l]; knn_d_saved[l] = b.knn_d[l];
         b.item_off[l] = off;
         if (l <= b.new_top) {
             const uint32_t s = ix->stride[l];
@@ -211,18 +214,16 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         off += b.items[l];
     }
     b.item_off[MAX_LEVELS] = off; b.total_items = off;
-    unsigned long long* ctr = ix->stats_on ? ix->counters : nullptr;
-    auto mark = [&]() { if (ix->build_trace) { cudaEvent_t e; if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ix->stream); ix->trace_ev.push_back(e); } } };
-    mark();
-    // The graph search of the batch (K4a, frozen graph) and its exact intra-batch neighbours (K1/K2/K1f) are independent:
-    // they run on two streams and join before the link step.
-    cudaStream_t ks = ix->build_overlap ? ix->side : ix->stream;
-    if (ix->build_overlap) { CU(cudaEventRecord(ix->fork_ev, ix->stream)); CU(cudaStreamWaitEvent(ks, ix->fork_ev, 0)); }
-    GraphView frozen = ix->view(first, b.new_top);
-    CU(launch_build_search(frozen, b, ix->efA, ix->dev, ctr, ix->stream));
-    mark();
+}
+
+// Exact intra-batch neighbours (K1/K2/K1f) of the batch on stream ks, into knn buffer set `buf`. They depend on the batch's
+// own rows only, not on the graph, so they may run any time after the rows are in place.
+vs_status batch_knn(vs_index* ix, uint32_t first, uint32_t count, int buf, cudaStream_t ks) {
+    BuildBatch b = ix->bb;
+    batch_shape(ix, first, count, b);
     for (int l = 0; l <= b.new_top; ++l) {
-        if (b.items[l] < 2) { b.knn_id[l] = nullptr; b.knn_d[l] = nullptr; continue; }
+        if (b.items[l] < 2) continue;
+        uint32_t* kid = ix->knn_set_id[buf][l]; float* kd = ix->knn_set_d[buf][l];
         const uint32_t s = ix->stride[l], fs = b.first_row[l] * s;
         ExactCorpus c{}; c.vecs = ix->vecs + (size_t)fs * ix->dpad; c.sqn = ix->sqn + fs; c.row_stride = (size_t)s * ix->dpad; c.row_step = s;
         c.first_slot = fs; c.n = b.items[l]; c.deleted = nullptr; c.slot_key = nullptr; c.n_slots = first + count;
@@ -232,21 +233,47 @@ vs_status insert_batch(vs_index* ix, uint32_t first, uint32_t count) {
         if (ix->build_tc && exact_tc_supported(c, q, k)) {   // big level-0 blocks: tensor-core scan + exact re-rank (same results)
             size_t want = exact_tc_scratch_bytes(q.nq, c.n, k + 1, ix->dpad, ix->dev.sm_count);
             if (want > ix->tc_scratch.n) {   // size it once for every batch shape up to max_batch: a cudaFree + cudaMalloc per growing batch cost up to 300 ms
-                for (uint32_t b = 4096; b <= ix->max_batch; b *= 2) want = std::max(want, exact_tc_scratch_bytes(b, b, KNN_BATCH + 1, ix->dpad, ix->dev.sm_count));
+                // (every tile count, not only powers of two: the plan's slice count is not monotonic in the batch size, and a
+                // 30 000-row batch that outgrew the scratch sized for 32 768 rows stalled the pipeline for 19 ms)
+                for (uint32_t bs = 4096; bs <= ix->max_batch; bs += 128) want = std::max(want, exact_tc_scratch_bytes(bs, bs, KNN_BATCH + 1, ix->dpad, ix->dev.sm_count));
                 want = std::max(want, exact_tc_scratch_bytes(ix->max_batch, ix->max_batch, KNN_BATCH + 1, ix->dpad, ix->dev.sm_count));
+                CU(cudaStreamSynchronize(ix->stream)); CU(cudaStreamSynchronize(ks));   // the scratch is about to move
             }
             CU(ix->tc_scratch.ensure(want));
             ExactScratch ts{ix->tc_scratch.p, ix->tc_scratch.n};
-            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], ts, sc, ix->dev, ks, &ix->tc_build_stats));
+            CU(launch_exact_tc(c, q, ix->metric, k, KNN_BATCH, kid, nullptr, kd, ts, sc, ix->dev, ks, &ix->tc_build_stats));
             continue;
         }
-        CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, knn_id_saved[l], nullptr, knn_d_saved[l], sc, ix->dev, ks));
+        CU(launch_exact(c, q, ix->metric, k, KNN_BATCH, kid, nullptr, kd, sc, ix->dev, ks));
     }
-    if (ix->build_overlap) { CU(cudaEventRecord(ix->join_ev, ks)); CU(cudaStreamWaitEvent(ix->stream, ix->join_ev, 0)); }
+    return VS_OK;
+}
+
+// K4a for slots [first, first + count): the batch's search on the frozen graph. `b` comes back filled for batch_link.
+vs_status batch_search(vs_index* ix, uint32_t first, uint32_t count, int buf, BuildBatch& b) {
+    b = ix->bb;   // scratch pointers
+    batch_shape(ix, first, count, b);
+    for (int l = 0; l < MAX_LEVELS; ++l) {
+        if (l > b.new_top || b.items[l] < 2) { b.knn_id[l] = nullptr; b.knn_d[l] = nullptr; }
+        else { b.knn_id[l] = ix->knn_set_id[buf][l]; b.knn_d[l] = ix->knn_set_d[buf][l]; }
+    }
+    auto mark = [&]() { if (ix->build_trace) { cudaEvent_t e; if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ix->stream); ix->trace_ev.push_back(e); } } };
+    mark();
+    GraphView frozen = ix->view(first, b.new_top);
+    CU(launch_build_search(frozen, b, ix->efA, ix->dev, ix->stats_on ? ix->counters : nullptr, ix->stream));
+    mark();
+    return VS_OK;
+}
+
+// K4b + K5: once the batch's exact neighbours are ready (`knn_ready`, null = already ordered on this stream), heuristic
+// selection and reverse-link merge.
+vs_status batch_link(vs_index* ix, const BuildBatch& b, cudaEvent_t knn_ready) {
+    auto mark = [&]() { if (ix->build_trace) { cudaEvent_t e; if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ix->stream); ix->trace_ev.push_back(e); } } };
+    if (knn_ready) CU(cudaStreamWaitEvent(ix->stream, knn_ready, 0));
     mark();
     CU(cudaMemsetAsync(ix->lt.n_edges, 0, 8, ix->stream));
-    GraphView linked = ix->view(first + count, b.new_top);
-    CU(launch_link(linked, b, ix->lt, ix->efpA, KNN_BATCH, ix->dev, ctr, ix->stream));
+    GraphView linked = ix->view(b.first_slot + b.count, b.new_top);
+    CU(launch_link(linked, b, ix->lt, ix->efpA, KNN_BATCH, ix->dev, ix->stats_on ? ix->counters : nullptr, ix->stream));
     mark();
     ix->st_build_batches++;
     return VS_OK;
@@ -285,15 +312,50 @@ vs_status flush_locked(vs_index* ix, const float* d_rows /* device rows or null 
     }
     CU(launch_row_prepare(d_rows, ix->vecs, ix->sqn, base, (uint32_t)n, ix->dims, ix->dpad, ix->stream));
     CU(cudaEventRecord(ix->ev0, ix->stream));
-    size_t done = 0;
-    while (done < n) {
+    // bootstrap block (all-pairs), then batches of at most 1/batch_div of the landed graph so
+    // that almost every candidate a new node needs is already linked (recall vs batch size: DESIGN.md)
+    std::vector<std::pair<uint32_t, uint32_t>> bl;
+    for (size_t done = 0; done < n;) {
         const uint32_t cur = base + (uint32_t)done;
-        // bootstrap block (all-pairs), then batches of at most 1/batch_div of the landed graph so
-        // that almost every candidate a new node needs is already linked (recall vs batch size: DESIGN.md)
         uint32_t bsz = cur == 0 ? 1024u : std::max(256u, cur / ix->batch_div);
         bsz = (uint32_t)std::min<size_t>({(size_t)bsz, (size_t)ix->max_batch, n - done});
-        vs_status s = insert_batch(ix, cur, bsz); if (s != VS_OK) return s;
-        done += bsz;
+        bl.emplace_back(cur, bsz); done += bsz;
+    }
+    if (!ix->build_overlap) {            // one stream: neighbours, search, link, batch after batch
+        for (auto& bt : bl) {
+            BuildBatch b;
+            vs_status s = batch_knn(ix, bt.first, bt.second, 0, ix->stream); if (s != VS_OK) return s;
+            s = batch_search(ix, bt.first, bt.second, 0, b); if (s != VS_OK) return s;
+            s = batch_link(ix, b, nullptr); if (s != VS_OK) return s;
+        }
+    } else {
+        // The exact intra-batch neighbours (K1/K2/K1f) need the batch's rows only, so they run on the side stream - next to the
+        // graph search of the same batch, and with build_pipeline = LA batches AHEAD: the neighbours of batch i+LA are enqueued while
+        // batch i searches and links (the persistent search kernel fills every SM, the link kernels leave room). LA+1 buffer sets
+        // rotate; a set is reused once the link step that read it has finished.
+        const int LA = ix->build_pipeline, NS = LA + 1;             // look-ahead in batches, buffer sets in rotation
+        bool linked_once[vs_index::KNN_SETS] = {};
+        CU(cudaEventRecord(ix->fork_ev, ix->stream));               // rows are in place (launch_row_prepare above)
+        CU(cudaStreamWaitEvent(ix->side, ix->fork_ev, 0));
+        auto enqueue_knn = [&](size_t i) -> vs_status {
+            const int buf = (int)(i % NS);
+            if (linked_once[buf]) CU(cudaStreamWaitEvent(ix->side, ix->link_done[buf], 0));
+            vs_status s = batch_knn(ix, bl[i].first, bl[i].second, buf, ix->side); if (s != VS_OK) return s;
+            CU(cudaEventRecord(ix->knn_done[buf], ix->side));
+            return VS_OK;
+        };
+        // Host order matters as much as stream order: a batch costs ~1 ms of host time to enqueue (the neighbour search alone is
+        // a dozen launches, tensor maps and attribute calls per level) against ~5 ms on the GPU, so the graph search of batch i
+        // goes to the GPU FIRST and the host prepares the side-stream work while it runs.
+        for (size_t i = 0; i < (size_t)LA && i < bl.size(); ++i) { vs_status s = enqueue_knn(i); if (s != VS_OK) return s; }
+        for (size_t i = 0; i < bl.size(); ++i) {
+            const int buf = (int)(i % NS);
+            BuildBatch b;
+            vs_status s = batch_search(ix, bl[i].first, bl[i].second, buf, b); if (s != VS_OK) return s;
+            if (i + LA < bl.size()) { s = enqueue_knn(i + LA); if (s != VS_OK) return s; }
+            s = batch_link(ix, b, ix->knn_done[buf]); if (s != VS_OK) return s;
+            CU(cudaEventRecord(ix->link_done[buf], ix->stream)); linked_once[buf] = true;
+        }
     }
     CU(cudaEventRecord(ix->ev1, ix->stream));
     CU(cudaStreamSynchronize(ix->stream));
@@ -308,8 +370,10 @@ vs_status flush_locked(vs_index* ix, const float* d_rows /* device rows or null 
             if (t > worst) { worst = t; worst_i = i; }
             if (i + 1 < nb) { cudaEventElapsedTime(&t, ix->trace_ev[4 * i + 3], ix->trace_ev[4 * i + 4]); gaps += t; }
         }
-        fprintf(stderr, "[vsann build trace] %zu batches: total %.1f ms = search %.1f + batch-knn %.1f + link %.1f + gaps %.1f; slowest batch #%zu %.2f ms\n",
-                nb, ms, ph[0], ph[1], ph[2], gaps, worst_i, worst);
+        float w3[3] = {0, 0, 0};
+        for (int k = 0; k < 3 && nb; ++k) cudaEventElapsedTime(&w3[k], ix->trace_ev[4 * worst_i + k], ix->trace_ev[4 * worst_i + k + 1]);
+        fprintf(stderr, "[vsann build trace] %zu batches: total %.1f ms = search %.1f + batch-knn %.1f + link %.1f + gaps %.1f; slowest batch #%zu %.2f ms (search %.2f, knn wait %.2f, link %.2f)\n",
+                nb, ms, ph[0], ph[1], ph[2], gaps, worst_i, worst, w3[0], w3[1], w3[2]);
         for (cudaEvent_t e : ix->trace_ev) cudaEventDestroy(e);
         ix->trace_ev.clear();
     }
@@ -400,6 +464,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
     if (const char* e = getenv("VSANN_SELECT_SMEM")) ix->dev.select_smem = atoi(e) != 0;
     if (const char* e = getenv("VSANN_ZERO_COPY")) ix->zero_copy = atoi(e) != 0;   // 0: always stage host queries with a copy
     if (const char* e = getenv("VSANN_COALESCE")) ix->coalesce = atoi(e) != 0;     // 0: every vs_search call is its own launch
+    if (const char* e = getenv("VSANN_BUILD_PIPELINE")) ix->build_pipeline = std::max(0, std::min(vs_index::KNN_SETS - 1, atoi(e)));   // batches of look-ahead; 0: a batch's neighbours next to its own graph search only
     if (const char* e = getenv("VSANN_BUILD_OVERLAP")) ix->build_overlap = atoi(e) != 0;   // 0: batch neighbours after the graph search, same stream
     if (const char* e = getenv("VSANN_BUILD_TRACE")) ix->build_trace = atoi(e) != 0;   // per-phase build timing on stderr
     if (const char* e = getenv("VSANN_BUILD_TC")) ix->build_tc = atoi(e) != 0;   // 0: FP32 tile kernel for the batch neighbours (A/B, profiling)
@@ -408,6 +473,7 @@ vs_status vs_index_create(const vs_options* o, vs_index** out) {
         CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&ix->side, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&ix->fork_ev, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ix->join_ev, cudaEventDisableTiming));
+        for (int e = 0; e < vs_index::KNN_SETS; ++e) { CU(cudaEventCreateWithFlags(&ix->knn_done[e], cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ix->link_done[e], cudaEventDisableTiming)); }
         CU(cudaEventCreate(&ix->ev0)); CU(cudaEventCreate(&ix->ev1)); CU(cudaEventCreateWithFlags(&ix->user_ev, cudaEventDisableTiming));
         CU(cudaMalloc(&ix->counters, 8 * sizeof(unsigned long long)));
         CU(cudaMemsetAsync(ix->counters, 0, 8 * sizeof(unsigned long long), ix->stream));
@@ -433,6 +499,7 @@ void vs_index_destroy(vs_index* ix) {
     ix->qpad.release(); ix->qdense.release(); ix->out_d.release(); ix->out_k.release();
     if (ix->ev0) cudaEventDestroy(ix->ev0); if (ix->ev1) cudaEventDestroy(ix->ev1); if (ix->user_ev) cudaEventDestroy(ix->user_ev);
     if (ix->fork_ev) cudaEventDestroy(ix->fork_ev); if (ix->join_ev) cudaEventDestroy(ix->join_ev);
+    for (int e = 0; e < vs_index::KNN_SETS; ++e) { if (ix->knn_done[e]) cudaEventDestroy(ix->knn_done[e]); if (ix->link_done[e]) cudaEventDestroy(ix->link_done[e]); }
     if (ix->side) { cudaStreamSynchronize(ix->side); cudaStreamDestroy(ix->side); }
     if (ix->stream) cudaStreamDestroy(ix->stream);
     if (ix->found_pin) cudaFreeHost(ix->found_pin); ix->found_d.release();
