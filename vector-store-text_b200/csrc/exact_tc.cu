@@ -681,7 +681,23 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     if (stats) stats->fp32_fallback += nf;
     if (nf == 0) return cudaSuccess;
     // what is left (fewer than k live candidates, overflow twice): FP32 tile kernel
-    if (q.self_step) {   // self-exclusion is positional: redo the whole block (insertion batches; rare)
+    if (q.self_step) {   // insertion batches: self-exclusion is positional (query i is slot self_first + i * self_step)
+        if (nf <= 16) {
+            // a handful of unproven rows: answer each as a one-query problem whose "position 0" is its own slot (the streaming
+            // scan, ~20 us each). Redoing the whole block through the FP32 tile kernel for ONE such row cost 17.8 ms in the
+            // 1M x 128 build (batch #89, 25 622 rows).
+            uint32_t ids[16];
+            TC_TRY(cudaMemcpyAsync(ids, S.fb_ids, (size_t)nf * 4, cudaMemcpyDeviceToHost, st));
+            TC_TRY(cudaStreamSynchronize(st));
+            for (uint32_t i = 0; i < nf; ++i) {
+                ExactQueries q1 = q;
+                q1.q = q.q + (size_t)ids[i] * q.stride; q1.nq = 1; q1.self_first = q.self_first + ids[i] * q.self_step;
+                TC_TRY(launch_exact(c, q1, metric, k, out_ld, out_slots ? out_slots + (size_t)ids[i] * out_ld : nullptr,
+                                    out_keys ? out_keys + (size_t)ids[i] * out_ld : nullptr, out_dist ? out_dist + (size_t)ids[i] * out_ld : nullptr,
+                                    fb_scratch, dev, st));
+            }
+            return cudaStreamSynchronize(st);
+        }
         e = launch_exact(c, q, metric, k, out_ld, out_slots, out_keys, out_dist, fb_scratch, dev, st);
         return e != cudaSuccess ? e : cudaStreamSynchronize(st);
     }
