@@ -503,6 +503,16 @@ def main():
     fn_host = getattr(lib, "vs_search_batch")
 
     def e2e_step():
+        if world > 1 and p2p:
+            # sharded serving path: the traversal kernel reads the pinned HOST queries in place (vs_search_batch_device accepts any
+            # device-accessible pointer; page-locked memory is one under UVA) and writes the shard's lists into symmetric memory,
+            # the fused gather + merge follows on the same stream, only the merged top-k goes back to the host
+            i, kp, dp = p2p.next_buffer()
+            g.search_device(nq, qh.data_ptr(), K_NN, kp, dp, ef=chosen, stream=stream)
+            p2p.merge(i, mk, md)
+            kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
+            torch.cuda.synchronize()
+            return
         stt = fn_host(g._h, nq, C.c_void_p(qh.data_ptr()), K_NN, chosen, 0, C.c_void_p(kh.data_ptr()), C.c_void_p(dh.data_ptr()), fh.ctypes.data_as(C.c_void_p))
         assert stt == 0
         if world > 1:   # results come back to the host per shard; merge on device as the serving rank would
