@@ -30,7 +30,14 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#if defined(__AVX2__) && defined(__FMA__)
+#include <immintrin.h>
+#define OVS_HAVE_SIMD 1
+#else
+#define OVS_HAVE_SIMD 0
+#endif
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <memory>
@@ -62,6 +69,47 @@ inline float l2sq_seq(const float* a, const float* b, size_t d) {
     for (size_t i = 0; i < d; ++i) { float t = a[i] - b[i]; acc = std::fmaf(t, t, acc); }
     return acc;
 }
+// 8-wide AVX2 + FMA distances with four independent accumulators: what a production CPU library (usearch links SimSIMD)
+// runs per distance. OPT-IN (ovs_set_simd): only the timed CPU baseline of bench.py uses it, so that the baseline is not
+// handicapped by the sequential chain above; every parity test keeps the sequential definition, and exact search always does.
+#if OVS_HAVE_SIMD
+inline float hsum8(__m256 v) {
+    __m128 s = _mm_add_ps(_mm256_castps256_ps128(v), _mm256_extractf128_ps(v, 1));
+    s = _mm_add_ps(s, _mm_movehl_ps(s, s));
+    s = _mm_add_ss(s, _mm_shuffle_ps(s, s, 1));
+    return _mm_cvtss_f32(s);
+}
+inline float dot_simd(const float* a, const float* b, size_t d) {
+    __m256 s0 = _mm256_setzero_ps(), s1 = s0, s2 = s0, s3 = s0; size_t i = 0;
+    for (; i + 32 <= d; i += 32) {
+        s0 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i), s0);
+        s1 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i + 8), _mm256_loadu_ps(b + i + 8), s1);
+        s2 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i + 16), _mm256_loadu_ps(b + i + 16), s2);
+        s3 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i + 24), _mm256_loadu_ps(b + i + 24), s3);
+    }
+    for (; i + 8 <= d; i += 8) s0 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i), s0);
+    float acc = hsum8(_mm256_add_ps(_mm256_add_ps(s0, s1), _mm256_add_ps(s2, s3)));
+    for (; i < d; ++i) acc = std::fmaf(a[i], b[i], acc);
+    return acc;
+}
+inline float l2sq_simd(const float* a, const float* b, size_t d) {
+    __m256 s0 = _mm256_setzero_ps(), s1 = s0, s2 = s0, s3 = s0; size_t i = 0;
+    for (; i + 32 <= d; i += 32) {
+        __m256 t0 = _mm256_sub_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i)), t1 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 8), _mm256_loadu_ps(b + i + 8));
+        __m256 t2 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 16), _mm256_loadu_ps(b + i + 16)), t3 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 24), _mm256_loadu_ps(b + i + 24));
+        s0 = _mm256_fmadd_ps(t0, t0, s0); s1 = _mm256_fmadd_ps(t1, t1, s1); s2 = _mm256_fmadd_ps(t2, t2, s2); s3 = _mm256_fmadd_ps(t3, t3, s3);
+    }
+    for (; i + 8 <= d; i += 8) { __m256 t = _mm256_sub_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i)); s0 = _mm256_fmadd_ps(t, t, s0); }
+    float acc = hsum8(_mm256_add_ps(_mm256_add_ps(s0, s1), _mm256_add_ps(s2, s3)));
+    for (; i < d; ++i) { float t = a[i] - b[i]; acc = std::fmaf(t, t, acc); }
+    return acc;
+}
+inline void prefetch_row(const float* v, size_t d) { for (size_t i = 0; i < d; i += 16) _mm_prefetch((const char*)(v + i), _MM_HINT_T0); }
+#else
+inline float dot_simd(const float* a, const float* b, size_t d) { return dot_seq(a, b, d); }
+inline float l2sq_simd(const float* a, const float* b, size_t d) { return l2sq_seq(a, b, d); }
+inline void prefetch_row(const float*, size_t) {}
+#endif
 inline float cos_from(float dot, float na, float nb) {
     if (na == 0.f && nb == 0.f) return 0.f;
     if (na == 0.f || nb == 0.f) return 1.f;
@@ -100,15 +148,25 @@ struct vs_index {
     std::mutex rng_mu;
     double mL = 0;
     unsigned threads = 1;
+    bool simd = false;               // ovs_set_simd: SIMD distances in the HNSW paths (timed CPU baseline only)
     std::atomic<uint64_t> c_sq{0}, c_sde{0}, c_sx{0}, c_bv{0}, c_bde{0};
 
     const float* vec(uint32_t s) const { return vecs.data() + (size_t)s * dims; }
-    float dist(const float* q, float qn, uint32_t s) const {
+    float dist_seq(const float* q, float qn, uint32_t s) const {   // the definition (exact search, every parity test)
         const float* v = vec(s);
         switch (metric) {
             case VS_METRIC_L2SQ: return l2sq_seq(q, v, dims);
             case VS_METRIC_IP: return 1.f - dot_seq(q, v, dims);
             default: return cos_from(dot_seq(q, v, dims), qn, sqn[s]);
+        }
+    }
+    float dist(const float* q, float qn, uint32_t s) const {       // HNSW build / search
+        if (!simd) return dist_seq(q, qn, s);
+        const float* v = vec(s);
+        switch (metric) {
+            case VS_METRIC_L2SQ: return l2sq_simd(q, v, dims);
+            case VS_METRIC_IP: return 1.f - dot_simd(q, v, dims);
+            default: return cos_from(dot_simd(q, v, dims), qn, sqn[s]);
         }
     }
     float qnorm(const float* q) const { return metric == VS_METRIC_COS ? dot_seq(q, q, dims) : 0.f; }
@@ -144,6 +202,7 @@ void search_layer(vs_index* ix, const float* q, float qn, std::vector<DistId>& e
         ++expansions;
         Node& n = *ix->nodes[c.s];
         { std::lock_guard<std::mutex> g(n.mu); nb = n.links[level]; }
+        if (ix->simd) for (uint32_t s : nb) if (vis.stamp[s] != vis.cur) prefetch_row(ix->vec(s), ix->dims);   // as usearch prefetches the neighbours of a node
         for (uint32_t s : nb) {
             if (vis.test_set(s)) continue;
             float d = ix->dist(q, qn, s); ++evals;
@@ -247,7 +306,7 @@ void hnsw_search(vs_index* ix, const float* q, size_t k, size_t ef, std::vector<
 void exact_search(vs_index* ix, const float* q, size_t k, std::vector<std::pair<float, uint64_t>>& out) {
     float qn = ix->qnorm(q); uint32_t n = ix->n_slots.load();
     out.clear(); out.reserve(ix->live.load());
-    for (uint32_t s = 0; s < n; ++s) if (!ix->deleted[s]) out.push_back({ix->dist(q, qn, s), ix->slot_key[s]});
+    for (uint32_t s = 0; s < n; ++s) if (!ix->deleted[s]) out.push_back({ix->dist_seq(q, qn, s), ix->slot_key[s]});
     size_t kk = std::min(k, out.size());
     std::partial_sort(out.begin(), out.begin() + kk, out.end());
     out.resize(kk);
@@ -284,6 +343,7 @@ vs_status ovs_index_create(const vs_options* o, vs_index** out) {
     ix->efS = o->expansion_search ? o->expansion_search : 64;
     if (ix->M < 2) ix->M = 2;
     ix->mL = 1.0 / std::log((double)ix->M);
+    if (const char* e = getenv("OVS_SIMD")) ix->simd = atoi(e) != 0 && OVS_HAVE_SIMD;   // for callers that only hold the function table (lib/actor_load)
     vs_status s = do_reserve(ix, o->capacity_hint ? o->capacity_hint : 1000000);  // usearch.rs:62,99
     if (s != VS_OK) { delete ix; return s; }
     *out = ix; return VS_OK;
@@ -291,6 +351,8 @@ vs_status ovs_index_create(const vs_options* o, vs_index** out) {
 void ovs_index_destroy(vs_index* ix) { delete ix; }
 
 vs_status ovs_set_threads(vs_index* ix, unsigned t) { if (!ix) return VS_ERR_INVALID; ix->threads = t ? t : 1; return VS_OK; }
+vs_status ovs_set_simd(vs_index* ix, int on) { if (!ix) return VS_ERR_INVALID; ix->simd = on != 0 && OVS_HAVE_SIMD; return VS_OK; }
+int ovs_have_simd(void) { return OVS_HAVE_SIMD; }
 vs_status ovs_set_seed(vs_index* ix, uint64_t seed) { if (!ix) return VS_ERR_INVALID; ix->rng.seed(seed); return VS_OK; }
 
 vs_status ovs_reserve(vs_index* ix, size_t cap) {

@@ -102,6 +102,7 @@ def load_library(path: str = None, prefix: str = "vs_"):
         sig.update({
             "set_threads": (C.c_int, [vp, C.c_uint]),
             "set_seed": (C.c_int, [vp, C.c_uint64]),
+            "set_simd": (C.c_int, [vp, C.c_int]),
             "distance": (C.c_float, [C.c_int, f32p, f32p, C.c_size_t]),
             "graph_search": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, f32p, vp, C.c_size_t, vp, C.c_uint32, f32p,
                                        C.c_size_t, C.c_size_t, vp, f32p, szp, szp, szp]),
@@ -271,6 +272,10 @@ class VsIndex:
     # oracle-only helpers
     def set_threads(self, t):
         self._check(self._fn("set_threads")(self._h, int(t)))
+
+    def set_simd(self, on=True):
+        """Oracle only: SIMD distances in its HNSW paths (bench.py's timed CPU baseline; parity tests keep the sequential chain)."""
+        self._check(self._fn("set_simd")(self._h, 1 if on else 0))
 
     def set_seed(self, s):
         self._check(self._fn("set_seed")(self._h, int(s)))
