@@ -99,16 +99,7 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
             RList<NL> L;
             rbeam_seed(S, L, (int)ef, cur, dcur);
             rbeam_level(g, 0, S, L, qn, evals, exps);
-#pragma unroll
-            for (int j = 0; j < NL; ++j) {
-                const uint32_t id = L.id[j] & ~EXPANDED;
-                const bool live = L.id[j] != NONE && !is_deleted(g, id);
-                const unsigned m = __ballot_sync(0xffffffffu, live);
-                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
-                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
-                nout += __popc(m);
-            }
-            if (nout > k) nout = k;
+            nout = L.emit_live(g, k, ko, dd);
         }
         for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
         ++done;
@@ -152,16 +143,7 @@ __global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : 2)) k_search_t(
             RList<NL> L;
             rbeam_seed(S, L, (int)ef, cur, dcur);
             tbeam_level<NL, CPL>(g, 0, S, T, Q, L, qn, evals, exps);
-#pragma unroll
-            for (int j = 0; j < NL; ++j) {
-                const uint32_t id = L.id[j] & ~EXPANDED;
-                const bool live = L.id[j] != NONE && !is_deleted(g, id);
-                const unsigned m = __ballot_sync(0xffffffffu, live);
-                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
-                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
-                nout += __popc(m);
-            }
-            if (nout > k) nout = k;
+            nout = L.emit_live(g, k, ko, dd);
         }
         for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
         ++done;
@@ -295,16 +277,7 @@ __global__ void __launch_bounds__(256) k_search_blk(const __grid_constant__ CUte
             }
         }
         if (warp == 0) {
-#pragma unroll
-            for (int j = 0; j < NL; ++j) {
-                const uint32_t id = L.id[j] & ~EXPANDED;
-                const bool live = L.id[j] != NONE && !is_deleted(g, id);
-                const unsigned m = __ballot_sync(0xffffffffu, live);
-                const uint32_t pos = nout + __popc(m & ((1u << lane) - 1u));
-                if (live && pos < k) { ko[pos] = g.slot_key[id]; dd[pos] = L.d[j]; }
-                nout += __popc(m);
-            }
-            if (nout > k) nout = k;
+            nout = L.emit_live(g, k, ko, dd);
         }
     }
     if (warp == 0) {
@@ -388,14 +361,7 @@ __global__ void __launch_bounds__(128, 6) k_build_search_r(GraphView g, BuildBat
             rbeam_level(g, l, S, L, qn, evals, exps);
             const uint32_t idx = slot / g.stride[l] - b.first_row[l];
             uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
-            uint32_t n = 0;
-#pragma unroll
-            for (int j = 0; j < NL; ++j) {
-                const int i = j * 32 + lane;
-                if (i < (int)efp) { ci[i] = L.id[j] == NONE ? NONE : (L.id[j] & ~EXPANDED); cd[i] = L.d[j]; }
-                n += __popc(__ballot_sync(0xffffffffu, L.id[j] != NONE));
-            }
-            for (int i = NL * 32 + lane; i < (int)efp; i += 32) { ci[i] = NONE; cd[i] = INFINITY; }
+            const uint32_t n = L.store_sorted(ci, cd, (int)efp);
             if (lane == 0) b.cand_n[l][idx] = n;
             if (l > 0) rbeam_reseed(S, L);
         }
@@ -437,14 +403,7 @@ __global__ void __launch_bounds__(128, VSANN_T_MINB) k_build_search_t(const __gr
             tbeam_level<NL, CPL>(g, l, S, T, Q, L, qn, evals, exps);
             const uint32_t idx = slot / g.stride[l] - b.first_row[l];
             uint32_t* ci = b.cand_id[l] + (size_t)idx * efp; float* cd = b.cand_d[l] + (size_t)idx * efp;
-            uint32_t n = 0;
-#pragma unroll
-            for (int j = 0; j < NL; ++j) {
-                const int i = j * 32 + lane;
-                if (i < (int)efp) { ci[i] = L.id[j] == NONE ? NONE : (L.id[j] & ~EXPANDED); cd[i] = L.d[j]; }
-                n += __popc(__ballot_sync(0xffffffffu, L.id[j] != NONE));
-            }
-            for (int i = NL * 32 + lane; i < (int)efp; i += 32) { ci[i] = NONE; cd[i] = INFINITY; }
+            const uint32_t n = L.store_sorted(ci, cd, (int)efp);
             if (lane == 0) b.cand_n[l][idx] = n;
             if (l > 0) rbeam_reseed(S, L);
         }
