@@ -640,6 +640,7 @@ def main():
     build["capacity_growths"] = st.get("reserve_calls")
     build["reserve_seconds"] = st.get("reserve_seconds")
     build["device_bytes"] = st.get("device_bytes")
+    build["tables_grow_in_place"] = st.get("tables_grow_in_place")
     qd = torch.from_numpy(q).to(dev)
     torch.cuda.synchronize()
     if rank == 0:

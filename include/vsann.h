@@ -12,7 +12,8 @@
  *   - all pointers are HOST memory unless the function name ends in `_device`
  *   - caller keeps ownership of every buffer; inputs are copied/staged before return
  *   - thread-safe: any number of host threads may call into one index concurrently
- *     (the reference holds the library under Arc<RwLock<_>>, usearch.rs:98,201-221,245,276,309)
+ *     (the reference holds the library under Arc<RwLock<_>>, usearch.rs:98,201-221,245,276,309);
+ *     searches do not wait for a running insertion batch: they read the part of the graph that has landed
  *   - the GPU library has NO CPU fallback: if no CUDA device is usable,
  *     vs_index_create fails with VS_ERR_CUDA.
  *
@@ -60,9 +61,16 @@ typedef struct vs_options {
     size_t expansion_add;     /* ef used while inserting                                    */
     size_t expansion_search;  /* default ef for vs_search (effective ef = max(ef, k))       */
     size_t capacity_hint;     /* initial reserve; 0 => 1 000 000 (usearch.rs:62,99)         */
-    int32_t device;           /* CUDA device ordinal of this shard (one index = one GPU)    */
+    int32_t device;           /* CUDA device ordinal (single-device index, n_devices <= 1)  */
     size_t max_batch;         /* insertion batch cap; 0 => library default                  */
-    uint64_t reserved[4];     /* must be zero                                               */
+    /* One index over several GPUs of one box, inside ONE process (the reference's actor holds one
+     * Arc<RwLock<usearch::Index>> - usearch.rs:98,105-136): n_devices in 2..8 => the index owns one shard per
+     * device_ids[i], shard = key % n_devices; adds and removes are routed, searches fan out
+     * on every device's own stream and a merge kernel on device_ids[0] reads the shards' result lists over
+     * NVLink peer mappings. 0 or 1 => a single shard on `device`. (These 32 bytes were `reserved[4]`.) */
+    uint8_t n_devices;
+    uint8_t device_ids[8];
+    uint8_t reserved[23];     /* must be zero                                               */
 } vs_options;
 
 /* Work counters; device-side counters are collected only when enabled with
@@ -90,6 +98,13 @@ typedef struct vs_stats {
     uint64_t exact_stream_queries; /* exact-mode queries answered by the HBM-streaming scan (batches of <= 16 queries) */
     uint64_t search_host_queries;  /* queries that came through vs_search / vs_search_batch (host buffers) ...              */
     uint64_t search_host_launches; /* ... and the launches that answered them: concurrent vs_search calls share a launch      */
+    uint64_t build_expansions;     /* beam pops of the insertion searches (device counter, with vs_set_stats)                 */
+    uint64_t reserve_calls;        /* capacity growths (usearch.rs:201-212) ...                                               */
+    double   reserve_seconds;      /* ... and the wall time they took                                                         */
+    uint64_t compactions;          /* rebuilds that dropped tombstoned slots (slot reuse, usearch.rs:214-221,245) ...         */
+    double   compact_seconds;      /* ... and the wall time they took                                                         */
+    uint32_t tables_grow_in_place; /* 1: tables are VMM-backed and grow without a copy or a new pointer                       */
+    uint32_t n_devices;            /* shards (GPUs) behind this index                                                         */
 } vs_stats;
 
 /* usearch::Index::new + reserve — usearch.rs:82-99 (called from create_index, :38-53). */
@@ -105,7 +120,10 @@ vs_status vs_add_batch(vs_index* index, size_t n, const uint64_t* keys, const fl
 /* Same, rows already resident in HBM on the index's device (keys stay on the host). */
 vs_status vs_add_batch_device(vs_index* index, size_t n, const uint64_t* keys, const float* d_vecs);
 
-/* usearch::Index::remove(key) — usearch.rs:215,245. Tombstone; count drops by one. */
+/* usearch::Index::remove(key) — usearch.rs:215,245. Tombstone; count drops by one. Does not flush staged adds
+ * (a staged add of the key is dropped). Once tombstones exceed a quarter of the slots the index compacts itself:
+ * live rows are gathered to the front and the graph is rebuilt, so slots (and HBM) stay bounded under the
+ * reference's replace-heavy ingest (usearch frees and reuses the slot, usearch.rs:214-221). */
 vs_status vs_remove(vs_index* index, uint64_t key);
 
 /* usearch::Index::search(&embedding, limit) -> Matches{keys, distances} — usearch.rs:276,288,298.
@@ -152,6 +170,16 @@ vs_status vs_merge_topk_device(int device, size_t parts, size_t nq, size_t k,
  * arrays of `parts` pointers. The caller orders the call after every shard's search (a cross-rank barrier). */
 vs_status vs_merge_topk_peers_device(int device, size_t parts, size_t nq, size_t k,
                                      const uint64_t* const* d_part_keys, const float* const* d_part_dist,
+                                     uint64_t* d_keys_out, float* d_dist_out, void* stream);
+
+/* The same with the cross-rank barrier INSIDE the merge kernel (one process per GPU, lists and flag words in symmetric
+ * memory): d_part_flags[p] is rank p's flag word as mapped on this device. The call follows the rank's own search on
+ * `stream`; the kernel publishes flag[my_part] = epoch (system-scope release) and waits until every peer's flag has
+ * reached `epoch` (system-scope acquire over NVLink) before it reads that peer's lists. Epochs increase by one per step;
+ * two alternating list buffers make one flag per rank sufficient. No separate barrier kernel, no all-gather. */
+vs_status vs_merge_topk_flags_device(int device, size_t parts, size_t nq, size_t k,
+                                     const uint64_t* const* d_part_keys, const float* const* d_part_dist,
+                                     uint32_t* const* d_part_flags, uint32_t my_part, uint32_t epoch,
                                      uint64_t* d_keys_out, float* d_dist_out, void* stream);
 
 /* Debug/verification: copy the level-`level` neighbour table to the host.

@@ -174,7 +174,8 @@ def test_traversal_matches_oracle_large_graph(vst, oracle_lib, ef, d, k):
     g.close()
 
 
-def test_incremental_adds_removes_replace(vst, oracle_lib):
+def test_incremental_adds_removes_replace(vst, oracle_lib, monkeypatch):
+    monkeypatch.setenv("VSANN_COMPACT_FRAC", "1")      # keep the tombstones (compaction has its own tests in test_gpu_mutations.py)
     n, d = 6000, 48
     x = make_data(n, d, 51, clustered=True); q = make_data(200, d, 52, clustered=True)
     g = vst.VsIndex(d, metric=1, capacity_hint=1000, max_batch=512)        # forces capacity growth + many batches

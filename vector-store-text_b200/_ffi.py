@@ -12,7 +12,7 @@ ABI_SYMBOLS = [
     "vs_index_create", "vs_index_destroy", "vs_add", "vs_add_batch", "vs_add_batch_device", "vs_remove",
     "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_count", "vs_capacity", "vs_reserve",
     "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_export_level",
-    "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
+    "vs_merge_topk_flags_device", "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
 ]
 
 
@@ -25,7 +25,8 @@ class Metric(enum.IntEnum):
 class VsOptions(C.Structure):
     _fields_ = [("dims", C.c_size_t), ("metric", C.c_int32), ("connectivity", C.c_size_t),
                 ("expansion_add", C.c_size_t), ("expansion_search", C.c_size_t), ("capacity_hint", C.c_size_t),
-                ("device", C.c_int32), ("max_batch", C.c_size_t), ("reserved", C.c_uint64 * 4)]
+                ("device", C.c_int32), ("max_batch", C.c_size_t), ("n_devices", C.c_uint8), ("device_ids", C.c_uint8 * 8),
+                ("reserved", C.c_uint8 * 23)]
 
 
 class VsStats(C.Structure):
@@ -35,7 +36,9 @@ class VsStats(C.Structure):
                 ("build_seconds", C.c_double), ("device_bytes", C.c_uint64), ("top_level", C.c_uint32),
                 ("dims", C.c_uint32), ("exact_tc_queries", C.c_uint64), ("exact_tc_fallback", C.c_uint64),
                 ("exact_tc_second_scan", C.c_uint64), ("exact_tc_scans", C.c_uint64), ("exact_tc_scan_seconds", C.c_double),
-                ("exact_stream_queries", C.c_uint64), ("search_host_queries", C.c_uint64), ("search_host_launches", C.c_uint64)]
+                ("exact_stream_queries", C.c_uint64), ("search_host_queries", C.c_uint64), ("search_host_launches", C.c_uint64),
+                ("build_expansions", C.c_uint64), ("reserve_calls", C.c_uint64), ("reserve_seconds", C.c_double),
+                ("compactions", C.c_uint64), ("compact_seconds", C.c_double), ("tables_grow_in_place", C.c_uint32), ("n_devices", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -94,6 +97,7 @@ def load_library(path: str = None, prefix: str = "vs_"):
             "search_batch_device": (C.c_int, [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_int, vp, vp, vp]),
             "merge_topk_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "merge_topk_peers_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
+            "merge_topk_flags_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp]),
             "export_level": (C.c_int, [vp, C.c_uint32, vp, szp, szp, vp, szp]),
             "index_save": (C.c_int, [vp, C.c_char_p]),
             "index_load": (C.c_int, [C.c_char_p, C.POINTER(VsOptions), C.POINTER(vp)]),
@@ -128,12 +132,17 @@ class VsIndex:
     """One index = one GPU shard (or one oracle instance). Thin, typed wrapper over the C ABI."""
 
     def __init__(self, dims, metric=Metric.COS, connectivity=0, expansion_add=0, expansion_search=0,
-                 capacity_hint=0, device=0, max_batch=0, lib=None):
+                 capacity_hint=0, device=0, max_batch=0, lib=None, devices=None):
+        """devices: list of CUDA ordinals => ONE index over several GPUs in this process (vs_options.n_devices / device_ids)."""
         self.lib = lib or load_library()
         self.p = self.lib._vs_prefix
         self.dims = int(dims)
         opt = VsOptions(dims=self.dims, metric=int(metric), connectivity=connectivity, expansion_add=expansion_add,
                         expansion_search=expansion_search, capacity_hint=capacity_hint, device=device, max_batch=max_batch)
+        if devices:
+            opt.n_devices = len(devices)
+            for i, dv in enumerate(devices):
+                opt.device_ids[i] = int(dv)
         h = C.c_void_p()
         self._h = None
         self._check(self._fn("index_create")(C.byref(opt), C.byref(h)))
@@ -288,6 +297,16 @@ def merge_topk_device(device, parts, nq, k, keys_in_ptr, dist_in_ptr, keys_out_p
     lib = lib or load_library()
     st = lib.vs_merge_topk_device(int(device), int(parts), int(nq), int(k), C.c_void_p(int(keys_in_ptr)), C.c_void_p(int(dist_in_ptr)),
                                   C.c_void_p(int(keys_out_ptr)), C.c_void_p(int(dist_out_ptr)), C.c_void_p(int(stream)) if stream else None)
+    if st != VS_OK:
+        raise VsError(st, lib.vs_last_error().decode())
+
+
+def merge_topk_flags_device(device, parts, nq, k, part_keys_ptr, part_dist_ptr, part_flags_ptr, my_part, epoch, keys_out_ptr, dist_out_ptr, stream=0, lib=None):
+    """Fused barrier + gather + merge: as merge_topk_peers_device, with each rank's flag word (a DEVICE array of `parts` pointers)."""
+    lib = lib or load_library()
+    st = lib.vs_merge_topk_flags_device(int(device), int(parts), int(nq), int(k), C.c_void_p(int(part_keys_ptr)), C.c_void_p(int(part_dist_ptr)),
+                                        C.c_void_p(int(part_flags_ptr)), int(my_part), int(epoch) & 0xFFFFFFFF,
+                                        C.c_void_p(int(keys_out_ptr)), C.c_void_p(int(dist_out_ptr)), C.c_void_p(int(stream)) if stream else None)
     if st != VS_OK:
         raise VsError(st, lib.vs_last_error().decode())
 

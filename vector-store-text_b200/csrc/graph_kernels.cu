@@ -558,12 +558,20 @@ __global__ void __launch_bounds__(128) k_select(GraphView g, BuildBatch b, LinkT
     if (counters && lane == 0) atomicAdd(&counters[3], (unsigned long long)evals);
 }
 
+// Every touched row gets a segment of `inbox` as long as the number of reverse edges it received (counted by k_select),
+// so no edge is ever dropped and the merged row is a function of the edge SET: the build is deterministic whatever the
+// arrival order (a fixed 32-entry inbox kept "the first 32 to arrive" and made hub rows differ from run to run).
+__global__ void k_inbox_alloc(LinkTables t) {
+    const uint32_t n = *t.n_touched;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        t.inbox_off[i] = atomicAdd(t.inbox_cursor, t.inbox_cnt[t.touched_row[i]]);
+}
 __global__ void k_inbox_fill(LinkTables t) {
     const uint32_t n = *t.n_edges;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
         const uint32_t ti = t.inbox_idx[t.edge_row[e]];
         const uint32_t pos = atomicAdd(&t.inbox_fill[ti], 1u);
-        if (pos < INBOX_CAP) t.inbox[(size_t)ti * INBOX_CAP + pos] = t.edge_src[e];
+        t.inbox[t.inbox_off[ti] + pos] = t.edge_src[e];
     }
 }
 
@@ -589,12 +597,14 @@ __global__ void __launch_bounds__(128) k_reverse_merge(GraphView g, LinkTables t
             const float d = warp_dist32(g, S.q4, vn, id, S.scr_id, S.scr_d, evals);
             slist_merge(S.L, d, id, S.scr_id, S.scr_d);
         }
-        {   // inbox
-            const uint32_t nin = min(t.inbox_fill[w], (uint32_t)INBOX_CAP);
-            uint32_t id = lane < nin ? t.inbox[(size_t)w * INBOX_CAP + lane] : NONE;
-            if (id == v) id = NONE;
-            const float d = warp_dist32(g, S.q4, vn, id, S.scr_id, S.scr_d, evals);
-            slist_merge(S.L, d, id, S.scr_id, S.scr_d);
+        {   // inbox: every reverse edge of this batch, 32 at a time (the list keeps the best 64 of row + inbox by (distance, id))
+            const uint32_t nin = t.inbox_cnt[r], off = t.inbox_off[w];
+            for (uint32_t c0 = 0; c0 < nin; c0 += 32) {
+                uint32_t id = c0 + lane < nin ? t.inbox[off + c0 + lane] : NONE;
+                if (id == v) id = NONE;
+                const float d = warp_dist32(g, S.q4, vn, id, S.scr_id, S.scr_d, evals);
+                slist_merge(S.L, d, id, S.scr_id, S.scr_d);
+            }
         }
         // count distinct candidates now in the list
         uint32_t n = 0;
@@ -675,10 +685,28 @@ __global__ void k_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint
 // no gathered copy in HBM. A dependent tournament over remote loads would pay the NVLink latency k times, so the warp first
 // pulls all parts x k candidates of its query into shared memory in one round of independent loads, then merges locally.
 // STAGED = false: lists too large for shared memory are read in place (same tournament as k_merge_topk).
+// flags != null: the cross-rank barrier is part of this kernel. Rank `my_part` publishes "my lists of step `epoch` are complete"
+// (they are: this kernel follows the rank's traversal kernel on its stream) with a system-scope release store into its flag word,
+// which every peer has mapped, and every block waits (system-scope acquire loads over NVLink) until each peer's flag has reached
+// `epoch` before it pulls that peer's lists: one launch after the traversal, no separate barrier kernel, no launch gap in between.
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+
 template <bool STAGED>
 __global__ void k_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* __restrict__ part_keys,
-                                  const float* const* __restrict__ part_dist, uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
+                                  const float* const* __restrict__ part_dist, uint32_t* const* __restrict__ flags, uint32_t my_part, uint32_t epoch,
+                                  uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
     extern __shared__ __align__(16) unsigned char msm[];
+    if (flags) {
+        if (threadIdx.x == 0) {
+            if (blockIdx.x == 0) { __threadfence_system(); st_release_sys(flags[my_part], epoch); }
+            for (uint32_t p = 0; p < parts; ++p) {
+                if (p == my_part) continue;
+                while ((int32_t)(ld_acquire_sys(flags[p]) - epoch) < 0) __nanosleep(100);
+            }
+        }
+        __syncthreads();
+    }
     const uint32_t warp = threadIdx.x >> 5, q = blockIdx.x * (blockDim.x >> 5) + warp, lane = lane_id();
     if (q >= nq) return;
     const uint32_t tot = parts * k;
@@ -952,6 +980,7 @@ cudaError_t launch_link(const GraphView& g, const BuildBatch& b, const LinkTable
     uint32_t maxb = dev.sm_count * 8; if (blocks > maxb) blocks = maxb;
     k_select<<<blocks, wpb * 32, smem, st>>>(g, b, t, efp, kbp, counters, kept_smem);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    k_inbox_alloc<<<dev.sm_count * 4, 256, 0, st>>>(t);
     k_inbox_fill<<<dev.sm_count * 4, 256, 0, st>>>(t);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     smem = warp_smem_bytes(g.dpad, 64, 32) * wpb;
@@ -968,7 +997,7 @@ cudaError_t launch_row_prepare(const float* d_src, float* vecs, float* sqn, uint
     if (n == 0) return cudaSuccess;
     const size_t total = (size_t)n * dpad;
     uint32_t blocks = (uint32_t)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
-    k_scatter_rows<<<blocks, 256, 0, st>>>(d_src, vecs, first, n, dims, dpad);
+    if (d_src) k_scatter_rows<<<blocks, 256, 0, st>>>(d_src, vecs, first, n, dims, dpad);   // null: the rows are already in the table (dims == dpad, copied straight from the host)
     k_row_norms<<<(n + 127) / 128, 128, 0, st>>>(vecs, sqn, first, n, dpad);
     return cudaGetLastError();
 }
@@ -1004,20 +1033,26 @@ cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uin
     return cudaGetLastError();
 }
 
-cudaError_t launch_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
-                                   uint64_t* keys_out, float* dist_out, cudaStream_t st) {
-    if (nq == 0 || k == 0 || parts == 0) return cudaSuccess;
+cudaError_t launch_merge_topk_flags(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
+                                    uint32_t* const* flags, uint32_t my_part, uint32_t epoch, uint64_t* keys_out, float* dist_out, cudaStream_t st) {
+    if (k == 0 || parts == 0) return cudaSuccess;
+    if (nq == 0 && !flags) return cudaSuccess;
     if (parts > 128) return cudaErrorInvalidValue;
     const uint32_t threads = 128, qpb = threads / 32;
     const size_t smem = (size_t)qpb * parts * k * 12;
+    const uint32_t blocks = std::max<uint32_t>(1, (nq + qpb - 1) / qpb);   // at least one block: the flag must be published even for an empty batch
     if (smem <= 96 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_merge_topk_ptrs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_merge_topk_ptrs<true><<<(nq + qpb - 1) / qpb, threads, smem, st>>>(parts, nq, k, part_keys, part_dist, keys_out, dist_out);
+        k_merge_topk_ptrs<true><<<blocks, threads, smem, st>>>(parts, nq, k, part_keys, part_dist, flags, my_part, epoch, keys_out, dist_out);
     } else {
-        k_merge_topk_ptrs<false><<<(nq + qpb - 1) / qpb, threads, 0, st>>>(parts, nq, k, part_keys, part_dist, keys_out, dist_out);
+        k_merge_topk_ptrs<false><<<blocks, threads, 0, st>>>(parts, nq, k, part_keys, part_dist, flags, my_part, epoch, keys_out, dist_out);
     }
     return cudaGetLastError();
+}
+cudaError_t launch_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
+                                   uint64_t* keys_out, float* dist_out, cudaStream_t st) {
+    return launch_merge_topk_flags(parts, nq, k, part_keys, part_dist, nullptr, 0, 0, keys_out, dist_out, st);
 }
 
 }  // namespace vsann

@@ -7,7 +7,6 @@
 namespace vsann {
 
 constexpr uint32_t WORK_RING_SLOTS = 256;
-constexpr uint32_t INBOX_CAP = 32;     // reverse edges one row can receive per batch
 constexpr uint32_t KNN_BATCH = 32;     // intra-batch exact neighbours merged into the candidates
 
 struct DeviceInfo {
@@ -47,15 +46,17 @@ struct LinkTables {
     uint32_t row_base[MAX_LEVELS];
     uint32_t* inbox_cnt;      // [total_rows]  edges registered this batch (0 between batches)
     uint32_t* inbox_idx;      // [total_rows]  -> touched index
-    uint32_t* n_edges;        // device scalars
+    uint32_t* n_edges;        // device scalars: n_edges, n_touched, inbox cursor (16 bytes, zeroed before every batch)
     uint32_t* n_touched;
+    uint32_t* inbox_cursor;
     uint32_t* edge_row;       // [edge_cap]
     uint32_t* edge_src;       // [edge_cap]
     uint32_t* touched_row;    // [edge_cap]
     uint32_t* touched_slot;   // [edge_cap]
     uint8_t* touched_level;   // [edge_cap]
-    uint32_t* inbox_fill;     // [edge_cap]
-    uint32_t* inbox;          // [edge_cap][INBOX_CAP]
+    uint32_t* inbox_fill;     // [edge_cap]   per touched row: entries written so far
+    uint32_t* inbox_off;      // [edge_cap]   per touched row: start of its segment in `inbox` (every edge has a place: no edge is dropped)
+    uint32_t* inbox;          // [edge_cap]   reverse-edge sources, one segment per touched row
 };
 
 // Exact (brute-force) search over a strided set of rows.
@@ -115,6 +116,8 @@ cudaError_t launch_row_prepare(const float* d_src, float* vecs, float* sqn, uint
 cudaError_t launch_tombstone(uint32_t* deleted, const uint32_t* d_slots, uint32_t n, cudaStream_t st);
 cudaError_t launch_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
                                    uint64_t* keys_out, float* dist_out, cudaStream_t st);
+cudaError_t launch_merge_topk_flags(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* part_keys, const float* const* part_dist,
+                                    uint32_t* const* flags, uint32_t my_part, uint32_t epoch, uint64_t* keys_out, float* dist_out, cudaStream_t st);
 cudaError_t launch_count_found(const uint64_t* keys, uint32_t nq, uint32_t k, uint32_t* found, cudaStream_t st);
 cudaError_t launch_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* keys_in, const float* dist_in,
                               uint64_t* keys_out, float* dist_out, cudaStream_t st);

@@ -92,7 +92,7 @@ struct Shard {
     std::shared_mutex tables;
     std::atomic<bool> flushing{false};
     // ---- tables --------------------------------------------------------------------------------------------
-    size_t capacity = 0, max_slots = 0; uint32_t n_slots = 0; int n_levels = 1;
+    size_t capacity = 0, max_slots = 0; uint32_t n_slots = 0; int n_levels = 1; std::atomic<size_t> cap_pub{0};
     VArr a_vecs, a_sqn, a_links0, a_linksU[MAX_LEVELS], a_slot_key, a_deleted, a_inbox_cnt, a_inbox_idx;
     uint32_t stride[MAX_LEVELS] = {}; size_t rows[MAX_LEVELS] = {};
     LinkTables lt{}; size_t total_rows = 0, edge_cap = 0;

@@ -17,34 +17,48 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from ._ffi import VsIndex, merge_topk_device, merge_topk_peers_device
+import os
+
+from ._ffi import VsIndex, merge_topk_device, merge_topk_flags_device, merge_topk_peers_device
 
 
 class PeerExchange:
-    """Fused gather + merge over peer memory for `nq` x `k` result lists per rank.
+    """Fused barrier + gather + merge over peer memory for `nq` x `k` result lists per rank.
 
-    Every rank owns two buffers in symmetric memory (keys u64 [nq, k] then dists f32 [nq, k]) that are mapped into
-    every peer. A step writes its shard's lists into buffer `turn` (the traversal kernel does so directly), calls
-    `merge()`: one cross-rank barrier on the current stream, then csrc k_merge_topk_ptrs pulls all peers' lists of a query
-    into shared memory in one round of NVLink loads and merges them. The buffers alternate, so one barrier per step is
-    enough: a rank that has passed barrier i+1 knows that every peer has finished merge i. Raises if symmetric memory
-    cannot be set up (callers fall back to all_gather)."""
+    Every rank owns two buffers in symmetric memory (keys u64 [nq, k] then dists f32 [nq, k]) and one flag word, all mapped
+    into every peer. A step writes its shard's lists into buffer `turn` (the traversal kernel does so directly) and calls
+    `merge()`: ONE launch of csrc k_merge_topk_ptrs, which publishes this rank's flag = step number (release, system scope),
+    waits for every peer's flag (acquire loads over NVLink), then pulls all peers' lists of a query into shared memory in one
+    round of NVLink loads and merges them. The buffers alternate, so one flag per rank is enough: a rank that has seen a
+    peer's flag i+1 knows that peer has finished merge i. `VSANN_P2P_FLAGS=0` selects the older form (torch's symmetric-memory
+    barrier kernel, then the merge kernel). Raises if symmetric memory cannot be set up (callers fall back to all_gather)."""
 
     def __init__(self, nq, k, device, group=None, lib=None):
         import torch.distributed._symmetric_memory as symm
         group = group or dist.group.WORLD
         self.nq, self.k, self.device, self.lib = nq, k, device, lib
         self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
         self.koff = nq * k * 8
         self.bufs = [symm.empty(nq * k * 12, dtype=torch.uint8, device=device) for _ in range(2)]
         self.hdls = [symm.rendezvous(b, group) for b in self.bufs]
         self.kptr = [torch.tensor([int(p) for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
         self.dptr = [torch.tensor([int(p) + self.koff for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
+        self.flags = symm.empty(64, dtype=torch.uint8, device=device)
+        self.flags.zero_()
+        self.fhdl = symm.rendezvous(self.flags, group)
+        self.fptr = torch.tensor([int(p) for p in self.fhdl.buffer_ptrs], dtype=torch.int64, device=device)
+        self.use_flags = os.environ.get("VSANN_P2P_FLAGS", "1") != "0"
+        self.epoch = 0
         self.turn = 0
+        torch.cuda.synchronize(device)
+        self.fhdl.barrier(channel=0)          # every rank's flag word is zero before anybody publishes
         torch.cuda.synchronize(device)
 
     def describe(self):
-        return "p2p loads from symmetric memory + fused merge kernel (one stream barrier per step)"
+        if self.use_flags:
+            return "p2p loads from symmetric memory, barrier fused into the merge kernel (release/acquire flags over NVLink): one launch after the traversal"
+        return "p2p loads from symmetric memory + fused merge kernel (torch symmetric-memory barrier kernel per step)"
 
     def next_buffer(self):
         """(index, keys device pointer, dists device pointer) of the buffer this step publishes into."""
@@ -59,6 +73,11 @@ class PeerExchange:
 
     def merge(self, i, mk, md):
         stream = torch.cuda.current_stream().cuda_stream
+        if self.use_flags:
+            self.epoch += 1
+            merge_topk_flags_device(self.device.index, self.world, self.nq, self.k, self.kptr[i].data_ptr(), self.dptr[i].data_ptr(),
+                                    self.fptr.data_ptr(), self.rank, self.epoch, mk.data_ptr(), md.data_ptr(), stream=stream, lib=self.lib)
+            return mk, md
         self.hdls[i].barrier(channel=0)
         merge_topk_peers_device(self.device.index, self.world, self.nq, self.k, self.kptr[i].data_ptr(), self.dptr[i].data_ptr(),
                                 mk.data_ptr(), md.data_ptr(), stream=stream, lib=self.lib)
