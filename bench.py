@@ -42,7 +42,7 @@ CONFIGS = {
                batches=[1024]),
     "c4": dict(name="configs[3] Deep-100M shape", n=100_000_000, d=96, metric="L2SQ", k=10, nq=10_000, scaling="strong", gen="device"),
     "c5": dict(name="configs[4] high-QPS serving", n=5_000_000, d=1536, metric="IP", k=100, nq=4096, scaling="strong", gen="device",
-               batches=[1, 8, 64, 512, 4096]),
+               batches=[1, 8, 64, 512, 4096], recall_sweep=True),
 }
 
 
@@ -540,7 +540,11 @@ def main():
     d, k, metric_name = cfg["d"], cfg["k"], cfg["metric"]
     metric = getattr(vst.Metric, metric_name)
     nq = args.nq or cfg["nq"]
-    n = shard_size(args, cfg, world)
+    # --single-process: ONE vs_index over args.gpus devices inside this process (vs_options.n_devices); same shards, same keys as torchrun
+    G = args.gpus if (args.single_process and world == 1 and args.gpus > 1) else 1
+    S = world * G                                   # shards behind the workload
+    n = shard_size(args, cfg, S)
+    n_local = n * G                                 # rows this process adds
     host_gen = cfg["gen"] == "host"
     grid = [args.ef] if args.ef else EF_GRID[k]
     # Every launch of the timed regions (flush write, events, search, merge, copies) goes to ONE explicit stream: the library
@@ -569,30 +573,35 @@ def main():
 
     def new_index(hint):
         return vst.VsIndex(d, metric=metric, connectivity=M, expansion_add=EF_ADD, expansion_search=EF_PARITY,
-                           capacity_hint=hint, device=local, lib=lib)
+                           capacity_hint=hint * G, device=local, lib=lib, devices=list(range(G)) if G > 1 else None)
 
     # ---- data: shard r holds keys i * world + r (shard = key % world) -------------
-    keys = np.arange(n, dtype=np.uint64) * world + rank
+    keys = np.arange(n, dtype=np.uint64) * world + rank if G == 1 else np.arange(n_local, dtype=np.uint64)
     hint = args.capacity_hint or n
     build = {"unit": "vectors/s"}
     x = None
     if host_gen:
-        x = gen(n, d, 42 + 1000 * rank, args.dist)
+        if G == 1:
+            x = gen(n, d, 42 + 1000 * rank, args.dist)
+        else:                                       # key i * G + r = row i of shard r, as under torchrun
+            x = np.empty((n_local, d), dtype=np.float32)
+            for r in range(G):
+                x[r::G] = gen(n, d, 42 + 1000 * r, args.dist)
         q = gen(nq, d, 43, args.dist)
         xd = torch.from_numpy(x).to(dev)
         torch.cuda.synchronize()
         # (1) untimed warm-up build (module load, allocator), (2) device-resident rows timed, (3) HOST rows through vs_add_batch on
         # the wall clock from the first add to count() == N - the index the searches below run on.
         if args.warmup > 0:
-            w = new_index(hint); w.add_batch_device(keys, xd.data_ptr(), n); w.close()
+            w = new_index(hint); w.add_batch_device(keys, xd.data_ptr(), n_local); w.close()
         w = new_index(hint)
         barrier()
         t0 = time.perf_counter()
-        w.add_batch_device(keys, xd.data_ptr(), n)
-        assert w.count() == n
+        w.add_batch_device(keys, xd.data_ptr(), n_local)
+        assert w.count() == n_local
         dev_wall = max_over_ranks(time.perf_counter() - t0)
         st = w.stats()
-        build["device_resident"] = {"vectors_per_s": n * world / max_over_ranks(st["build_seconds"]), "seconds_device": max_over_ranks(st["build_seconds"]),
+        build["device_resident"] = {"vectors_per_s": n * S / max_over_ranks(dev_wall if G > 1 else st["build_seconds"]), "seconds_device": max_over_ranks(st["build_seconds"]),
                                     "seconds_wall": dev_wall, "rows": "already in HBM (vs_add_batch_device)"}
         w.close()
         del xd
@@ -601,14 +610,15 @@ def main():
         barrier()
         t0 = time.perf_counter()
         step_rows = 1 << 18                     # the caller hands over 262 144 rows per call, as an ingest loop would
-        for a in range(0, n, step_rows):
-            b = min(n, a + step_rows)
+        step_rows *= G
+        for a in range(0, n_local, step_rows):
+            b = min(n_local, a + step_rows)
             g.add_batch(keys[a:b], xh[a:b].numpy())
-        assert g.count() == n
+        assert g.count() == n_local
         build_wall = max_over_ranks(time.perf_counter() - t0)
         st = g.stats()
-        build.update({"vectors_per_s": n * world / build_wall, "seconds_wall": build_wall, "seconds_device": max_over_ranks(st["build_seconds"]),
-                      "batches": st["build_batches"], "h2d_bytes": n * d * 4 + n * 8,
+        build.update({"vectors_per_s": n * S / build_wall, "seconds_wall": build_wall, "seconds_device": max_over_ranks(st["build_seconds"]),
+                      "batches": st["build_batches"], "h2d_bytes": n_local * d * 4 + n_local * 8,
                       "definition": "wall clock from the first vs_add_batch (pinned HOST rows, H2D inside) to vs_count() == N"})
         del xh
     else:
@@ -617,11 +627,11 @@ def main():
         rows = DeviceRows(torch, dev, d, 42 + 1000 * rank, args.dist, normalise)
         qd_full = DeviceRows(torch, dev, d, 43, args.dist, normalise).next(nq)
         g = new_index(hint)
-        chunk = min(n, 4_000_000)
+        chunk = min(n_local, 4_000_000)
         barrier()
         wall = 0.0
-        for a in range(0, n, chunk):
-            b = min(n, a + chunk)
+        for a in range(0, n_local, chunk):
+            b = min(n_local, a + chunk)
             blk = rows.next(b - a)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
@@ -629,11 +639,11 @@ def main():
             wall += time.perf_counter() - t0
             del blk
             if rank == 0 and (a // chunk) % 5 == 0:
-                log(f"built {b} / {n} rows per shard, {b / wall / 1e6:.2f} M vectors/s so far")
-        assert g.count() == n
+                log(f"built {b} / {n_local} rows in this process, {b / wall / 1e6:.2f} M vectors/s so far")
+        assert g.count() == n_local
         build_wall = max_over_ranks(wall)
         st = g.stats()
-        build.update({"vectors_per_s": n * world / build_wall, "seconds_wall": build_wall, "seconds_device": max_over_ranks(st["build_seconds"]),
+        build.update({"vectors_per_s": n * S / build_wall, "seconds_wall": build_wall, "seconds_device": max_over_ranks(st["build_seconds"]),
                       "batches": st["build_batches"],
                       "definition": "wall clock of the vs_add_batch_device calls (rows generated in HBM chunk by chunk; generation not timed) up to vs_count() == N"})
         q = qd_full.cpu().numpy()
@@ -665,7 +675,8 @@ def main():
         except Exception as e:   # noqa: BLE001
             print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]}); using NCCL all_gather", file=sys.stderr)
             p2p = None
-    exchange = (p2p.describe() if p2p else "nccl all_gather + merge kernel") if world > 1 else "none"
+    exchange = (p2p.describe() if p2p else "nccl all_gather + merge kernel") if world > 1 else (
+        f"one vs_index over {G} devices in one process: fan-out on {G} streams, merge kernel on device 0 over peer mappings" if G > 1 else "none")
 
     def local_search(ef, exact=False, nb=None, off=0):
         b = nb or nq
@@ -759,6 +770,25 @@ def main():
     if rank == 0:
         log(f"search: ef={chosen} recall={sweep.get(chosen)} {ms:.4f} ms per step ({nq / ms / 1e3:.2f} M queries/s), kernel {ms_kernel:.4f} ms")
 
+    # ---- recall sweep (configs[4]: "brute-force exact vs HNSW recall sweep"): every ef of the grid, recall + QPS + gathered bytes/s ----
+    recall_sweep = None
+    if cfg.get("recall_sweep") or os.environ.get("VSANN_BENCH_SWEEP"):
+        recall_sweep = {}
+        for ef in grid:
+            try:
+                g.set_stats(True); g.reset_stats()
+                r = recall(keys_of(search_step(ef)), truth)
+                sv = g.stats(); g.set_stats(False)
+            except vst.VsError as e:
+                recall_sweep[str(ef)] = f"unsupported: {e.message}"
+                break
+            t = timed(lambda: search_step(ef), max(3, args.steps // 4), 1, mark=False)
+            evq = sv["search_dist_evals"] / max(1, sv["search_queries"]); exq = sv["search_expansions"] / max(1, sv["search_queries"])
+            recall_sweep[str(ef)] = {"recall_at_k": round(r, 4), "ms_per_step": t, "qps": nq / t * 1e3, "kernel_dist_evals_per_query": evq,
+                                     "gathered_gbs_per_gpu": (evq * d * 4 + exq * 2 * M * 4) * nq / t / 1e6}
+            if rank == 0:
+                log(f"sweep ef={ef}: recall {r:.4f} {nq / t / 1e3:.3f} M queries/s, gathered {recall_sweep[str(ef)]['gathered_gbs_per_gpu']:.0f} GB/s per GPU")
+
     by_batch = {}
     for b in cfg.get("batches", []):
         if b <= nq and world == 1:
@@ -849,7 +879,7 @@ def main():
             pass
         hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
         row_bytes = 2 * M * 4
-        if host_gen:
+        if host_gen and G == 1:
             ev, ex = algorithmic_counts(vst, g, x, q, chosen, k)
             alg_src = "oracle beam (ovs_graph_search) on the GPU-built graph, 200-query sample"
         else:
@@ -863,7 +893,7 @@ def main():
         build_alg = None
         if not args.no_cpu:
             log("CPU baseline: building the oracle index ...")
-            if host_gen and world == 1:
+            if host_gen and S == 1:
                 cpu_n = args.cpu_n or n
                 cpu = CpuIndex(vst, d, metric_name, k, cpu_n)
                 cpu.add(keys[:cpu_n], x[:cpu_n])
@@ -896,7 +926,7 @@ def main():
                   "at_own_smallest_ef": {"ef_search": cpick, "recall_at_k": ctab.get(cpick), "value": nq / float(np.mean(t_own))},
                   "recall_by_ef": ctab, "build_vectors_per_s": cpu.n / cpu.build_s, "build_seconds": cpu.build_s,
                   "build_dist_evals_per_vector": cst["build_dist_evals"] / max(1, cpu.n), "dist_evals_per_query": cev, "expansions_per_query": cex}
-            if host_gen and world == 1 and cpu.n == n:
+            if host_gen and S == 1 and cpu.n == n:
                 g_at = sweep.get(chosen)
                 parity_at_bench = {"ef_search": chosen, "gpu_recall_at_k": g_at, "oracle_recall_at_k": round(c_at_gpu_ef, 4),
                                    "gpu_minus_oracle": round(g_at - c_at_gpu_ef, 4), "pass": bool(g_at >= c_at_gpu_ef - 0.01),
@@ -914,7 +944,7 @@ def main():
             # algorithmic bytes per inserted vector: every distance evaluation of the sequential algorithm gathers one row (d x 4 B);
             # link rows: one level-0 row written + M reverse rows read and rewritten (2M x 4 B each)
             bpv = build_alg * d * 4 + (1 + 2 * M) * row_bytes
-            b_ach = bpv * n * world / build["seconds_wall"] / 1e9 / world      # per GPU
+            b_ach = bpv * n / build["seconds_wall"] / 1e9      # per GPU
             build["roofline"] = {"bound": "hbm", "kernels": "k_build_search_t + k_select + k_reverse_merge + batch-kNN", "achieved": b_ach, "peak": hbm_peak,
                                  "unit": "GB/s", "frac": b_ach / hbm_peak, "bytes_per_vector": bpv, "dist_evals_per_vector": build_alg,
                                  "source": build_alg_src, "denominator": "wall seconds of the build (host rows, H2D inside)", "peak_source": peak_src}
@@ -922,7 +952,7 @@ def main():
         traffic = None
         try:   # DRAM bytes per launch of the search kernel from the newest committed ncu --set full capture at this ef (profiles/)
             tj = json.load(open(os.path.join(ROOT, "profiles", "r02_k_search_traffic.json")))
-            if world == 1 and tj.get("ef") == chosen and tj.get("config", "c2") == args.config and tj.get("dist", "clustered") == args.dist:
+            if S == 1 and tj.get("ef") == chosen and tj.get("config", "c2") == args.config and tj.get("dist", "clustered") == args.dist:
                 traffic = tj["dram_bytes_per_launch"]
         except Exception:
             pass
@@ -940,15 +970,16 @@ def main():
                                   "peak_source": "TF32 = half the measured bf16 burst rate (MEASURED_PEAKS.json bf16_tflops / 2)",
                                   "flops_per_launch": 2.0 * nq * n * d}}
         extra = {}
-        if host_gen and world == 1 and not args.no_extra and args.dist == "clustered":
+        if host_gen and S == 1 and not args.no_extra and args.dist == "clustered":
             extra["iid_gaussian"] = iid_block(args, vst, torch, lib, local, dev, ts, cfg, not args.no_cpu)
-        if world == 1 and not args.no_extra and not args.no_cpu and args.config == "c2":
+        if S == 1 and not args.no_extra and not args.no_cpu and args.config == "c2":
             extra["via_actor"] = via_actor_leg(vst, True)
-        total = n * world
+        total = n * S
         line = {
-            "metric": "ann_qps_at_recall95", "value": nq / (ms * 1e-3), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "metric": "ann_qps_at_recall95", "value": nq / (ms * 1e-3), "unit": "queries/s", "n_gpus": S, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config_dict(args, cfg, world),
+            "dtype": "f32", "data": "synthetic", "config": config_dict(args, cfg, S),
+            "process_model": "one process, one vs_index over %d devices" % G if G > 1 else ("one process per GPU (torchrun)" if world > 1 else "one process, one GPU"),
             "operating_point": {"ef_search": chosen, "recall_at_k": sweep.get(chosen), "recall_target_reached": reached,
                                 "criterion": "smallest ef reaching the target on a shard searched alone, max over ranks (the same criterion at every N)",
                                 "ef_sweep_recall_shard_alone": sweep_local, "ef_sweep_recall": sweep,
@@ -958,14 +989,14 @@ def main():
             "value_definition": ("queries answered per second against the whole corpus of corpus_total vectors "
                                  "(weak scaling: the corpus grows N x at fixed per-GPU work, so the ideal curve is FLAT; see shard_queries_per_s)"
                                  if cfg["scaling"] == "weak" else "queries answered per second against the whole corpus (split over the ranks)"),
-            "shard_queries_per_s": world * nq / (ms * 1e-3), "vectors_searched_per_s": total * nq / (ms * 1e-3),
+            "shard_queries_per_s": S * nq / (ms * 1e-3), "vectors_searched_per_s": total * nq / (ms * 1e-3),
             "parity_point": {"ef_search": parity_ef, "recall_at_k": sweep.get(parity_ef), "qps": nq / (ms_parity * 1e-3)},
             "parity_at_bench": parity_at_bench,
             "build": build,
             "e2e": {"value": nq / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12,
                     "ms_per_step": e2e_ms, "recall_at_k": e2e_recall},
-            "gpu_launches": args.steps * (1 if world == 1 else 2),   # per step: k_search_t (+ the merge kernel after the exchange)
-            "by_batch": by_batch or None,
+            "gpu_launches": args.steps * (1 if S == 1 else (G + 1 if G > 1 else 2)),   # per step: k_search_t per shard (+ the merge kernel after the exchange)
+            "by_batch": by_batch or None, "recall_sweep": recall_sweep,
             "exact": exact,
             "roofline": {"bound": "hbm", "kernel": "k_search_t", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel_ms": ms_kernel,
