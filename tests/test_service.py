@@ -98,12 +98,17 @@ def _post(url, obj):
 @pytest.mark.parametrize("native", [False, True])
 def test_integration_kat_over_http(vst, oracle_lib, native):
     """tests/integration/usearch.rs:20-135 with the HTTP client of tests/integration/httpclient.rs."""
+    run_integration_kat(vst, oracle_lib, native)
+
+
+def run_integration_kat(vst, lib, native):
+    """The KAT itself, over any backend exporting include/vsann.h (the oracle here, libvsann.so in tests/test_gpu_service.py)."""
     from vector_store_text_b200.service import DbEmbedding, Engine, HttpServer, ItemsMonitor
 
     def factory(index_id):
         if native:
-            return vst.NativeActor(index_id, 3, metric=vst.Metric.COS, capacity_hint=100, threads=1, lib=oracle_lib)
-        return vst.IndexActor(index_id, 3, metric=vst.Metric.COS, capacity_hint=100, lib=oracle_lib)
+            return vst.NativeActor(index_id, 3, metric=vst.Metric.COS, capacity_hint=100, threads=1, lib=lib)
+        return vst.IndexActor(index_id, 3, metric=vst.Metric.COS, capacity_hint=100, lib=lib)
 
     engine = Engine(factory)
     srv = HttpServer(engine, pk_columns=lambda index_id: ["pk", "ck"])
