@@ -93,3 +93,31 @@ def test_tc_selected_by_size_and_skipped_for_large_k(vst, oracle_lib, monkeypatc
     same(g, o, q, 10)
     assert g.stats()["exact_tc_queries"] == 256
     g.close()
+
+
+def test_exact_search_on_a_user_stream_does_not_synchronise(vst, oracle_lib, monkeypatch):
+    """include/vsann.h: vs_search_batch_device(stream != NULL) returns without synchronising - in exact mode too: the second scan and
+    the fallback are driven by counters that stay on the device. The call must come back while the GPU is still working."""
+    import torch
+    monkeypatch.setenv("VSANN_EXACT_TC", "1")
+    n, d, nq, k = 400000, 128, 8192, 10
+    x = make_data(n, d, 61); q = make_data(nq, d, 62)
+    g = vst.VsIndex(d, metric=1, capacity_hint=n, connectivity=2, expansion_add=8)
+    g.add_batch(np.arange(n, dtype=np.uint64), x)
+    dev = torch.device("cuda", 0)
+    qd = torch.from_numpy(q).to(dev)
+    ok = torch.empty((nq, k), dtype=torch.int64, device=dev); od = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    st = torch.cuda.Stream(device=dev)
+    g.search_device(nq, qd.data_ptr(), k, ok.data_ptr(), od.data_ptr(), exact=True, stream=st.cuda_stream)   # warm-up (scratch allocation)
+    st.synchronize()
+    pending = 0
+    for _ in range(5):
+        done = torch.cuda.Event()
+        g.search_device(nq, qd.data_ptr(), k, ok.data_ptr(), od.data_ptr(), exact=True, stream=st.cuda_stream)
+        done.record(st)
+        pending += not done.query()          # still running when the call has returned
+        st.synchronize()
+    assert pending >= 4, "the exact path must not wait for the GPU"
+    want, _, _ = g.search(q[:64], k, exact=True)
+    assert np.array_equal(ok.cpu().numpy().view(np.uint64)[:64], want)
+    g.close()

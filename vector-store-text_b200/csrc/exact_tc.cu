@@ -39,6 +39,7 @@ constexpr int EPI_COLS = BN / (EPI_WARPS / 4);   // columns one epilogue warp sc
 constexpr int R_MAX = 16;              // sampled keys kept per (query, slice)
 constexpr int SAMPLE_STRIDE = 32;      // large corpora: every 32nd tile is sampled (small ones: Plan::stride)
 constexpr uint32_t TMEM_COLS = 512;
+constexpr uint32_t R2_MAX = 1024;      // queries the second (proven-threshold) scan serves at most; more than that go to the FP32 fallback
 
 // dynamic shared memory (after rounding the base up to 1024 B)
 struct __align__(16) Ctrl {
@@ -120,6 +121,7 @@ struct ScanArgs {
     uint32_t n_tiles, tiles_per_slice, sample_stride;
     float* samp;                                 // SAMPLE: [slices * EPI_WARPS / 4][nq_pad][R_MAX] ascending
     const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
+    const uint32_t* n_active; uint32_t active_cap;                    // second scan: the query count lives on the device (null = nq)
 };
 
 // (a, b) of one corpus row: key = a * dot + b
@@ -144,6 +146,9 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     const uint32_t smem_s = s32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t q0 = blockIdx.x * BM, slice = blockIdx.y;
+    // second scan: launched for the largest query count it may see; CTAs past the count the first round left on the device leave at once
+    uint32_t nq_eff = a.nq;
+    if (a.n_active) { nq_eff = min(*a.n_active, a.active_cap); if (q0 >= nq_eff) return; }
     const uint32_t t_begin = slice * a.tiles_per_slice, t_end = min(a.n_tiles, t_begin + a.tiles_per_slice);
     const uint32_t t_step = EMIT ? 1u : a.sample_stride;
     const uint32_t t_first = EMIT ? t_begin : ((t_begin + a.sample_stride - 1) / a.sample_stride) * a.sample_stride;
@@ -223,7 +228,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
         // ===== epilogue: thread = one query row of the accumulator =====
         // warp w owns TMEM lanes 32 (w % 4) .. +31 (hardware rule) and the column half w / 4
         const uint32_t row = (uint32_t)(warp & 3) * 32 + lane, half = (uint32_t)warp >> 2, q = q0 + row;
-        const bool qok = q < a.nq;
+        const bool qok = q < nq_eff;
         float tau = -INFINITY;
         if (EMIT && qok) tau = a.tau[q];
         float top[R_MAX];
@@ -395,8 +400,11 @@ struct RerankArgs {
     // round 1 only: queries whose proof failed but whose k-th distance is known go to a second scan with
     // tau2 = key(dk + 2 eps) (a superset of the true top-k by construction)
     uint32_t* n_r2; uint32_t* r2_ids; float* r2_tau; float* r2_qn;
-    uint32_t* n_fb; uint32_t* fb_ids;                                  // queries only the FP32 kernel can answer
+    uint32_t* n_fb; uint32_t* fb_ids;                                  // queries only the FP32 fallback can answer
+    const uint32_t* n_active;                                          // second round: number of queries, on the device (null = nq)
+    uint32_t r2_cap;                                                   // second round: at most this many queries (the rest goes to the fallback)
 };
+__device__ __forceinline__ uint32_t rerank_nq(const RerankArgs& a) { return a.n_active ? min(*a.n_active, a.nq) : a.nq; }
 
 // Exact distances of the emitted candidates: grid (cap / 128, nq), one warp per 32 candidates. Each lane owns one
 // candidate and runs the oracle's sequential fmaf chain over the dimensions; rows are staged through a
@@ -405,6 +413,7 @@ __global__ void __launch_bounds__(128) k_tc_exact_dist(RerankArgs a) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t q = blockIdx.x, cblk = blockIdx.y;   // queries on x: batches above 65535 queries
+    if (q >= rerank_nq(a)) return;
     const uint32_t cnt = min(a.cnt[q], a.cap);
     if (cblk * 128u >= cnt) return;                          // whole block past the end
     float* qs = reinterpret_cast<float*>(sm);
@@ -447,7 +456,7 @@ __global__ void __launch_bounds__(128) k_tc_select(RerankArgs a, Less less) {
     extern __shared__ __align__(16) unsigned char sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
     const uint32_t q = blockIdx.x * wpb + warp;
-    if (q >= a.nq) return;
+    if (q >= rerank_nq(a)) return;
     unsigned char* base = sm + (size_t)warp * ((size_t)a.kp * 16 + 256);
     SList L;
     L.ld = reinterpret_cast<float*>(base); L.ld2 = L.ld + a.kp; L.li = reinterpret_cast<uint32_t*>(L.ld2 + a.kp); L.li2 = L.li + a.kp;
@@ -483,36 +492,98 @@ __global__ void __launch_bounds__(128) k_tc_select(RerankArgs a, Less less) {
         else if (a.metric == IP) tau2 = t2d - 1.f;
         else tau2 = (t2d - 1.f) * sqrtf(qn);
         // (a truncated candidate set still bounds the k-th distance from above, so overflow is no obstacle here)
-        if (a.n_r2 && full && (a.metric != COS || qn > 0.f) && isfinite(tau2)) {
-            const uint32_t i = atomicAdd(a.n_r2, 1u);
-            a.r2_ids[i] = gq; a.r2_tau[i] = tau2; a.r2_qn[i] = qn;
-        } else {
-            a.fb_ids[atomicAdd(a.n_fb, 1u)] = gq;
-        }
+        uint32_t i = 0xFFFFFFFFu;
+        if (a.n_r2 && full && (a.metric != COS || qn > 0.f) && isfinite(tau2)) i = atomicAdd(a.n_r2, 1u);
+        if (i < a.r2_cap) { a.r2_ids[i] = gq; a.r2_tau[i] = tau2; a.r2_qn[i] = qn; }
+        else a.fb_ids[atomicAdd(a.n_fb, 1u)] = gq;
     }
 }
 
 // gather / scatter for the queries that go to the FP32 kernel
-__global__ void k_tc_gather_queries(const float* __restrict__ q, size_t q_stride, uint32_t dpad, const uint32_t* __restrict__ flagged, uint32_t nf, float* __restrict__ out) {
-    const size_t total = (size_t)nf * dpad;
+__global__ void k_tc_gather_queries(const float* __restrict__ q, size_t q_stride, uint32_t dpad, const uint32_t* __restrict__ flagged, const uint32_t* __restrict__ n_dev, uint32_t cap,
+                                    float* __restrict__ out) {
+    const size_t total = (size_t)min(*n_dev, cap) * dpad;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
         out[i] = q[(size_t)flagged[i / dpad] * q_stride + (i % dpad)];
 }
-__global__ void k_tc_scatter_results(const uint64_t* __restrict__ keys, const float* __restrict__ dist, uint32_t ld, const uint32_t* __restrict__ flagged, uint32_t nf,
-                                     uint64_t* __restrict__ out_keys, float* __restrict__ out_dist) {
-    const size_t total = (size_t)nf * ld;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t o = (size_t)flagged[i / ld] * ld + (i % ld);
-        if (out_keys) out_keys[o] = keys[i];
-        if (out_dist) out_dist[o] = dist[i];
+// The queries neither round could prove (fewer than k live candidates, or a candidate list that overflowed twice: thousands of
+// exact ties): a plain FP32 scan with the oracle's sequential fmaf chain, one BLOCK per flagged query, driven by the count the
+// select kernels left on the device - launched unconditionally, it leaves at once when that count is zero, so the host never has
+// to read a counter back (no stream synchronisation anywhere in the exact path). Tiles of 256 rows go through a transposed shared
+// tile (coalesced loads, thread-per-row chains); rows that can still enter the top-k are merged into the block's sorted list.
+template <class Less>
+__global__ void __launch_bounds__(256) k_tc_fallback(RerankArgs a, uint32_t n_rows, Less less) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ uint32_t nbuf; __shared__ float worst;
+    const uint32_t nf = *a.n_fb;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    float* qs = reinterpret_cast<float*>(sm);
+    float* tile = qs + a.dpad;
+    float* bd = tile + 256 * 33;
+    uint32_t* bi = reinterpret_cast<uint32_t*>(bd + 256);
+    SList L;
+    L.ld = reinterpret_cast<float*>(bi + 256); L.ld2 = L.ld + a.kp; L.li = reinterpret_cast<uint32_t*>(L.ld2 + a.kp); L.li2 = L.li + a.kp;
+    uint32_t* scr_id = L.li2 + a.kp; float* scr_d = reinterpret_cast<float*>(scr_id + 32);
+    L.cap = (int)a.k; L.capp = (int)a.kp;
+    for (uint32_t f = blockIdx.x; f < nf; f += gridDim.x) {
+        const uint32_t gq = a.fb_ids[f];
+        __syncthreads();
+        for (uint32_t c = tid; c < a.dpad; c += blockDim.x) qs[c] = a.q[(size_t)gq * a.q_stride + c];
+        if (warp == 0) slist_init(L);
+        if (tid == 0) { nbuf = 0; worst = INFINITY; }
+        __syncthreads();
+        const float qn = a.qn[gq];
+        const uint32_t self = a.self_step ? a.self_first + gq * a.self_step : NONE;
+        for (uint32_t r0 = 0; r0 < n_rows; r0 += 256) {
+            const uint32_t row = r0 + tid, slot = a.first_slot + row;
+            bool valid = row < n_rows && slot != self;
+            if (valid && a.deleted && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) valid = false;
+            float acc = 0.f;
+            for (uint32_t kc = 0; kc < a.dpad; kc += 32) {
+                __syncthreads();
+#pragma unroll 4
+                for (int it = 0; it < 32; ++it) {
+                    const int idx = it * 256 + tid, rr = idx >> 5, cc = idx & 31;
+                    const uint32_t r = r0 + rr;
+                    tile[rr * 33 + cc] = (r < n_rows && kc + cc < a.dpad) ? __ldg(a.vecs + (size_t)r * a.dpad + kc + cc) : 0.f;
+                }
+                __syncthreads();
+                const uint32_t kend = min(32u, a.dpad - kc);
+                if (a.metric == L2SQ) { for (uint32_t i = 0; i < kend; ++i) { const float d = qs[kc + i] - tile[tid * 33 + i]; acc = fmaf(d, d, acc); } }
+                else { for (uint32_t i = 0; i < kend; ++i) acc = fmaf(qs[kc + i], tile[tid * 33 + i], acc); }
+            }
+            const float d = valid ? finish_metric(a.metric, acc, qn, a.metric == COS ? a.sqn[row] : 0.f) : INFINITY;
+            const bool ok = valid && d <= worst;                       // ties are admitted: the key order decides in the merge
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            uint32_t base = 0;
+            if (lane == 0 && m) base = atomicAdd(&nbuf, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (ok) { const uint32_t pos = base + __popc(m & ((1u << lane) - 1u)); bd[pos] = d; bi[pos] = slot; }
+            __syncthreads();
+            const uint32_t nb = nbuf;
+            if (nb && warp == 0) {
+                for (uint32_t b0 = 0; b0 < nb; b0 += 32) {
+                    const bool on = b0 + lane < nb;
+                    slist_merge(L, on ? bd[b0 + lane] : INFINITY, on ? bi[b0 + lane] : NONE, scr_id, scr_d, less);
+                }
+                if (lane == 0) { worst = L.ld[a.k - 1]; nbuf = 0; }
+            }
+            __syncthreads();
+        }
+        if (warp == 0) {
+            for (uint32_t i = lane; i < a.out_ld; i += 32) {
+                const uint32_t id = i < a.k ? L.li[i] : NONE;
+                if (a.out_slots) a.out_slots[(size_t)gq * a.out_ld + i] = id;
+                if (a.out_keys) a.out_keys[(size_t)gq * a.out_ld + i] = id == NONE ? 0xFFFFFFFFFFFFFFFFull : a.slot_key[id];
+                if (a.out_dist) a.out_dist[(size_t)gq * a.out_ld + i] = (i < a.k && id != NONE) ? L.ld[i] : INFINITY;
+            }
+        }
     }
 }
 
-
-__global__ void k_tc_scatter_slots(const uint32_t* __restrict__ slots, uint32_t ld, const uint32_t* __restrict__ flagged, uint32_t nf, uint32_t* __restrict__ out) {
-    const size_t total = (size_t)nf * ld;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
-        out[(size_t)flagged[i / ld] * ld + (i % ld)] = slots[i];
+// second_scan += number of queries that needed the second round, fallback += number the FP32 fallback answered (vs_get_stats)
+__global__ void k_tc_stats(const uint32_t* __restrict__ ctr, unsigned long long* __restrict__ dst) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) { dst[0] += ctr[0]; dst[1] += ctr[2]; }
 }
 
 // ---- host side ---------------------------------------------------------------------------------
@@ -643,6 +714,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     r.cand = S.cand; r.cand_d = S.cand_d; r.cnt = S.cnt; r.tau = S.tau; r.max_xn_bits = S.ctr + 1; r.out_keys = out_keys; r.out_slots = out_slots; r.out_dist = out_dist; r.out_ld = out_ld;
     r.self_first = q.self_first; r.self_step = q.self_step;
     r.n_r2 = S.ctr; r.r2_ids = S.r2_ids; r.r2_tau = S.r2_tau; r.r2_qn = S.r2_qn; r.n_fb = S.ctr + 2; r.fb_ids = S.fb_ids;
+    r.n_active = nullptr; r.r2_cap = std::min<uint32_t>(q.nq, R2_MAX);
     k_tc_exact_dist<<<dim3(q.nq, (p.cap + 127) / 128), 128, dsmem, st>>>(r);
     auto select = [&](const RerankArgs& ra, uint32_t nqs) {
         if (c.slot_key) k_tc_select<LessByKey><<<(nqs + 3) / 4, 128, ssmem, st>>>(ra, LessByKey{c.slot_key, c.n_slots});
@@ -650,73 +722,51 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     };
     select(r, q.nq);
     TC_TRY(cudaGetLastError());
-    uint32_t ctr[4] = {0, 0, 0, 0};
-    TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
-    TC_TRY(cudaStreamSynchronize(st));
-    const uint32_t n2 = ctr[0];
-    if (stats) { stats->queries += q.nq; stats->second_scan += n2; stats->scans++; }
-    if (timing) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) stats->scan_ms += ms; }
-    if (ev0) cudaEventDestroy(ev0);
-    if (ev1) cudaEventDestroy(ev1);
+    if (stats) { stats->queries += q.nq; stats->scans++; }
 
-    if (n2 > 0) {
-        // second scan for the unproven queries: tau2 = key(dk + 2 eps) emits a superset of the true top-k
-        k_tc_gather_queries<<<std::min<uint32_t>(n2, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.r2_ids, n2, S.gq);
-        const Plan p2 = make_plan(n2, c.n, kplan, q.dpad, dev.sm_count);
+    // Second round and fallback are launched UNCONDITIONALLY; how many queries they have to serve is read on the device
+    // (S.ctr[0] = unproven queries with a proven threshold, S.ctr[2] = queries for the FP32 fallback). With nothing to do their
+    // CTAs leave at once (~20 us for the lot), and the host never waits: vs_search_batch_device(exact = 1, stream) returns
+    // before the work completes, and an insertion pipeline that asks for a batch's neighbours keeps enqueuing.
+    {
+        const uint32_t cap2 = std::min<uint32_t>(q.nq, R2_MAX);
+        const Plan p2 = make_plan(cap2, c.n, kplan, q.dpad, dev.sm_count);
+        k_tc_gather_queries<<<std::min<uint32_t>(cap2, 256u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.r2_ids, S.ctr, cap2, S.gq);
         CUtensorMap mapQ2;
-        if (!make_map(&mapQ2, S.gq, n2, q.dpad, q.dpad, BM)) return cudaErrorNotSupported;
-        TC_TRY(cudaMemsetAsync(S.cnt, 0, (size_t)n2 * 4, st));
+        if (!make_map(&mapQ2, S.gq, cap2, q.dpad, q.dpad, BM)) return cudaErrorNotSupported;
+        TC_TRY(cudaMemsetAsync(S.cnt, 0, (size_t)cap2 * 4, st));
         ScanArgs a2 = a;
-        a2.nq = n2; a2.nq_pad = p2.nq_pad; a2.n_tiles = p2.n_tiles; a2.tiles_per_slice = p2.tiles_per_slice; a2.tau = S.r2_tau;
+        a2.nq = cap2; a2.nq_pad = p2.nq_pad; a2.n_tiles = p2.n_tiles; a2.tiles_per_slice = p2.tiles_per_slice; a2.tau = S.r2_tau;
+        a2.n_active = S.ctr; a2.active_cap = cap2;
         k_tc_scan<true><<<dim3(p2.nqt, p2.slices), THREADS, SMEM_BYTES, st>>>(mapQ2, mapX, a2);
         RerankArgs r2 = r;
-        r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = n2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr;
-        k_tc_exact_dist<<<dim3(n2, (p.cap + 127) / 128), 128, dsmem, st>>>(r2);
-        select(r2, n2);
+        r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = cap2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr; r2.n_active = S.ctr; r2.r2_cap = 0;
+        k_tc_exact_dist<<<dim3(cap2, (p.cap + 127) / 128), 128, dsmem, st>>>(r2);
+        select(r2, cap2);
         TC_TRY(cudaGetLastError());
-        TC_TRY(cudaMemcpyAsync(ctr, S.ctr, 16, cudaMemcpyDeviceToHost, st));
-        TC_TRY(cudaStreamSynchronize(st));
-    }
-    const uint32_t nf = ctr[2];
-    if (stats) stats->fp32_fallback += nf;
-    if (nf == 0) return cudaSuccess;
-    // what is left (fewer than k live candidates, overflow twice): FP32 tile kernel
-    if (q.self_step) {   // insertion batches: self-exclusion is positional (query i is slot self_first + i * self_step)
-        if (nf <= 16) {
-            // a handful of unproven rows: answer each as a one-query problem whose "position 0" is its own slot (the streaming
-            // scan, ~20 us each). Redoing the whole block through the FP32 tile kernel for ONE such row cost 17.8 ms in the
-            // 1M x 128 build (batch #89, 25 622 rows).
-            uint32_t ids[16];
-            TC_TRY(cudaMemcpyAsync(ids, S.fb_ids, (size_t)nf * 4, cudaMemcpyDeviceToHost, st));
-            TC_TRY(cudaStreamSynchronize(st));
-            for (uint32_t i = 0; i < nf; ++i) {
-                ExactQueries q1 = q;
-                q1.q = q.q + (size_t)ids[i] * q.stride; q1.nq = 1; q1.self_first = q.self_first + ids[i] * q.self_step;
-                TC_TRY(launch_exact(c, q1, metric, k, out_ld, out_slots ? out_slots + (size_t)ids[i] * out_ld : nullptr,
-                                    out_keys ? out_keys + (size_t)ids[i] * out_ld : nullptr, out_dist ? out_dist + (size_t)ids[i] * out_ld : nullptr,
-                                    fb_scratch, dev, st));
-            }
-            return cudaStreamSynchronize(st);
+        // what is left (fewer than k live candidates, overflow twice, more than R2_MAX unproven queries): the FP32 fallback
+        const size_t fsmem = (size_t)q.dpad * 4 + 256 * 33 * 4 + 256 * 8 + (size_t)p.kp * 16 + 256;
+        if (fsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
+        const uint32_t fblocks = std::min<uint32_t>(q.nq, (uint32_t)dev.sm_count * 2u);
+        if (c.slot_key) {
+            TC_TRY(cudaFuncSetAttribute(k_tc_fallback<LessByKey>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            k_tc_fallback<LessByKey><<<fblocks, 256, fsmem, st>>>(r, c.n, LessByKey{c.slot_key, c.n_slots});
+        } else {
+            TC_TRY(cudaFuncSetAttribute(k_tc_fallback<LessById>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            k_tc_fallback<LessById><<<fblocks, 256, fsmem, st>>>(r, c.n, LessById());
         }
-        e = launch_exact(c, q, metric, k, out_ld, out_slots, out_keys, out_dist, fb_scratch, dev, st);
-        return e != cudaSuccess ? e : cudaStreamSynchronize(st);
+        if (stats && stats->dev) k_tc_stats<<<1, 32, 0, st>>>(S.ctr, stats->dev);
+        TC_TRY(cudaGetLastError());
     }
-    uint64_t* gk = nullptr; float* gd = nullptr; uint32_t* gs = nullptr;
-    TC_TRY(cudaMalloc(&gk, (size_t)nf * out_ld * 8));
-    if ((e = cudaMalloc(&gd, (size_t)nf * out_ld * 4)) != cudaSuccess) { cudaFree(gk); return e; }
-    if (out_slots && (e = cudaMalloc(&gs, (size_t)nf * out_ld * 4)) != cudaSuccess) { cudaFree(gk); cudaFree(gd); return e; }
-    k_tc_gather_queries<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(q.q, q.stride, q.dpad, S.fb_ids, nf, S.gq);
-    ExactQueries sub = q; sub.q = S.gq; sub.stride = q.dpad; sub.nq = nf;
-    e = launch_exact(c, sub, metric, k, out_ld, gs, out_keys ? gk : nullptr, gd, fb_scratch, dev, st);
-    if (e == cudaSuccess) {
-        k_tc_scatter_results<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gk, gd, out_ld, S.fb_ids, nf, out_keys, out_dist);
-        if (out_slots) k_tc_scatter_slots<<<std::min<uint32_t>(nf, 1024u), 256, 0, st>>>(gs, out_ld, S.fb_ids, nf, out_slots);
-        e = cudaGetLastError();
+    (void)fb_scratch;
+    if (timing) {   // profiling mode only (vs_set_stats): the scan kernel's own duration needs the events to have completed
+        TC_TRY(cudaStreamSynchronize(st));
+        float ms = 0.f; if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) stats->scan_ms += ms;
     }
-    const cudaError_t e2 = cudaStreamSynchronize(st);
-    cudaFree(gk); cudaFree(gd); cudaFree(gs);
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    return cudaSuccess;
 #undef TC_TRY
-    return e != cudaSuccess ? e : e2;
 }
 
 }  // namespace vsann

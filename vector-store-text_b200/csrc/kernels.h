@@ -97,6 +97,7 @@ struct TcStats {                    // host-side counters of the tensor-core exa
     uint64_t queries = 0, fp32_fallback = 0, second_scan = 0, scans = 0;
     double scan_ms = 0;             // device time of the full (emit) scans, measured with events when time_scan is set
     bool time_scan = false;
+    unsigned long long* dev = nullptr;   // device counters {second-scan queries, fallback queries}, accumulated by the exact path itself (it never syncs to read them)
 };
 // Tensor-core (tcgen05 TF32 + exact FP32 re-rank) form of launch_exact for contiguous corpora; same results.
 bool exact_tc_supported(const ExactCorpus& c, const ExactQueries& q, uint32_t k);

@@ -770,6 +770,7 @@ vs_status Shard::create(const ShardOptions& o, Shard** out) {
         CU(cudaMalloc(&sh->counters, 8 * sizeof(unsigned long long)));
         CU(cudaMemsetAsync(sh->counters, 0, 8 * sizeof(unsigned long long), sh->stream));
         CU(cudaMalloc(&sh->dev.work_ring, WORK_RING_SLOTS * sizeof(uint32_t)));
+        sh->tc_stats.dev = sh->counters + 5;
         const size_t ms = sh->max_slots; const bool v = sh->use_vmm;
         sh->a_vecs.init(o.device, ms * sh->dpad * 4, v); sh->a_sqn.init(o.device, ms * 4, v); sh->a_links0.init(o.device, ms * sh->W0 * 4, v);
         sh->a_slot_key.init(o.device, ms * 8, v); sh->a_deleted.init(o.device, ((ms + 31) / 32) * 4 + 64, v);
@@ -820,7 +821,7 @@ vs_status Shard::get_stats(vs_stats* o) {
     o->build_vectors = st_build_vectors; o->build_dist_evals = c[3]; o->build_batches = st_build_batches; o->build_expansions = c[4];
     o->build_seconds = st_build_seconds; o->device_bytes = device_bytes + build_scratch.n + exact_scratch.n + tc_scratch.n;
     o->top_level = (uint32_t)top; o->dims = dims;
-    o->exact_tc_queries = tc_stats.queries; o->exact_tc_fallback = tc_stats.fp32_fallback; o->exact_tc_second_scan = tc_stats.second_scan;
+    o->exact_tc_queries = tc_stats.queries; o->exact_tc_fallback = c[6]; o->exact_tc_second_scan = c[5];
     o->exact_tc_scans = tc_stats.scans; o->exact_tc_scan_seconds = tc_stats.scan_ms * 1e-3;
     o->exact_stream_queries = st_stream_queries; o->search_host_queries = st_search_calls; o->search_host_launches = st_search_launches;
     o->reserve_calls = st_reserve_calls; o->reserve_seconds = st_reserve_seconds; o->compactions = st_compactions; o->compact_seconds = st_compact_seconds;
@@ -834,7 +835,7 @@ vs_status Shard::reset_stats() {
     CU(cudaMemsetAsync(counters, 0, 8 * sizeof(unsigned long long), sstream));
     CU(cudaStreamSynchronize(sstream));
     st_build_vectors = 0; st_build_batches = 0; st_build_seconds = 0; st_stream_queries = 0; st_search_calls = 0; st_search_launches = 0;
-    { const bool t = tc_stats.time_scan; tc_stats = TcStats(); tc_stats.time_scan = t; }
+    { const bool t = tc_stats.time_scan; tc_stats = TcStats(); tc_stats.time_scan = t; tc_stats.dev = counters + 5; }
     return VS_OK;
 }
 
