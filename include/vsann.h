@@ -57,7 +57,10 @@ typedef enum vs_metric { VS_METRIC_COS = 0, VS_METRIC_L2SQ = 1, VS_METRIC_IP = 2
 typedef struct vs_options {
     size_t dims;              /* Dimensions (lib.rs:147); must be > 0                       */
     int32_t metric;           /* vs_metric                                                  */
-    size_t connectivity;      /* M: level-0 rows hold 2M links, upper levels M              */
+    size_t connectivity;      /* M: level-0 rows hold 2M links, upper levels M. 2..16 (0 => 16): a level-0 row is
+                               * at most 32 links, one per lane of the traversing warp; larger values are refused
+                               * with VS_ERR_UNSUPPORTED (the reference passes its newtype through unbounded,
+                               * lib.rs:164, but only ever uses the crate default)                              */
     size_t expansion_add;     /* ef used while inserting                                    */
     size_t expansion_search;  /* default ef for vs_search (effective ef = max(ef, k))       */
     size_t capacity_hint;     /* initial reserve; 0 => 1 000 000 (usearch.rs:62,99)         */

