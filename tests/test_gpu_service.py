@@ -27,7 +27,10 @@ def test_out_of_order_ingest_through_lww_into_the_gpu_actor(vst):
     ts = rng.permutation(nmsg) + 1                                     # distinct write times
     is_del = rng.random(nmsg) < 0.05
     order = rng.permutation(nmsg)                                      # delivery order != write order
-    actor = vst.NativeActor("ks.items", d, metric=vst.Metric.L2SQ, capacity_hint=10000, threads=4, lib=vst.load_library())
+    # ONE worker thread: the actor (like the reference, src/index/usearch.rs:118-131) gives no ordering guarantee between messages in
+    # flight - with T workers an accepted "add, remove, add" of one key may run as "add, add, remove" - so a test that predicts the
+    # final state must have them processed in order.
+    actor = vst.NativeActor("ks.items", d, metric=vst.Metric.L2SQ, capacity_hint=10000, threads=1, lib=vst.load_library())
     mon = ItemsMonitor(actor)
     newest = {}
     for i in order:
