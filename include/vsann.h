@@ -185,6 +185,31 @@ vs_status vs_merge_topk_flags_device(int device, size_t parts, size_t nq, size_t
                                      uint32_t* const* d_part_flags, uint32_t my_part, uint32_t epoch,
                                      uint64_t* d_keys_out, float* d_dist_out, void* stream);
 
+/* ---- allocation-free brute force -------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Exact top-k of
+ * every query over a caller-held device corpus - the arithmetic and the ordering of vs_search_batch(exact = 1):
+ * one sequential fmaf chain per (query, row), results ascending by (distance, key) - with its scratch (per-chunk
+ * partial top-k lists) in a static device array of VS_NOALLOC_SCRATCH_BYTES that every GPU loading the library
+ * holds until exit. The call allocates nothing: no cudaMalloc / cudaFree / allocating library routine; the first
+ * call on a device asks the array's address once (cudaGetSymbolAddress) - make that call outside a capture.
+ *   d_vecs     n x dims f32 row-major, device memory on `device`; d_keys: n u64 keys or NULL (key of row r = r)
+ *   d_queries  nq x dims f32; d_keys_out / d_dist_out: nq x k, unused tail entries UINT64_MAX / +inf
+ *   stream     a cudaStream_t; NULL = the default stream, synchronised before returning
+ * Limits (VS_ERR_UNSUPPORTED / VS_ERR_DIMS with a message naming the limit): k <= VS_NOALLOC_MAX_K,
+ * dims <= VS_NOALLOC_MAX_DIMS, nq x roundup32(k) <= VS_NOALLOC_MAX_QUERY_K (e.g. 512 queries at k <= 32,
+ * 64 at k = 256), nq <= 65535, n < 2^31; no tombstones (the corpus is the caller's).
+ * Every call shares the one array and finds the previous call's contents there; nothing in it needs clearing
+ * (a call writes every word it later reads). Calls that OVERLAP on the GPU race on it: serialise them. */
+#define VS_NOALLOC_MAX_K 256
+#define VS_NOALLOC_MAX_DIMS 4096
+#define VS_NOALLOC_MAX_QUERY_K 16384
+#define VS_NOALLOC_SCRATCH_BYTES (8u << 20)
+vs_status vs_exact_search_noalloc_device(int device, int32_t metric, size_t dims, size_t n,
+                                         const float* d_vecs, const uint64_t* d_keys,
+                                         size_t nq, const float* d_queries, size_t k,
+                                         uint64_t* d_keys_out, float* d_dist_out, void* stream);
+
 /* Debug/verification: copy the level-`level` neighbour table to the host.
  * links_out holds n_rows x row_width u32 slot ids (UINT32_MAX = empty);
  * slot_keys_out (may be NULL) holds the u64 key of each of the `slots` slots.

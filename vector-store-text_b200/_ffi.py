@@ -12,7 +12,7 @@ ABI_SYMBOLS = [
     "vs_index_create", "vs_index_destroy", "vs_add", "vs_add_batch", "vs_add_batch_device", "vs_remove",
     "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_count", "vs_capacity", "vs_reserve",
     "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_export_level",
-    "vs_merge_topk_flags_device", "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
+    "vs_merge_topk_flags_device", "vs_exact_search_noalloc_device", "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
 ]
 
 
@@ -98,6 +98,7 @@ def load_library(path: str = None, prefix: str = "vs_"):
             "merge_topk_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "merge_topk_peers_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "merge_topk_flags_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp]),
+            "exact_search_noalloc_device": (C.c_int, [C.c_int, C.c_int32, C.c_size_t, C.c_size_t, vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp, vp]),
             "export_level": (C.c_int, [vp, C.c_uint32, vp, szp, szp, vp, szp]),
             "index_save": (C.c_int, [vp, C.c_char_p]),
             "index_load": (C.c_int, [C.c_char_p, C.POINTER(VsOptions), C.POINTER(vp)]),

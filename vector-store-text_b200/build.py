@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.environ.get("VSANN_LIB_OUT") or os.path.join(HERE, "lib", "libvsann.so")
-SOURCES = ["index.cu", "shard.cu", "graph_kernels.cu", "exact_kernels.cu", "exact_tc.cu"]
+SOURCES = ["index.cu", "shard.cu", "graph_kernels.cu", "exact_kernels.cu", "exact_tc.cu", "noalloc.cu"]
 HEADERS = ["common.cuh", "beam.cuh", "rbeam.cuh", "tbeam.cuh", "tmap.h", "kernels.h", "shard.cuh", "vmm.h", "flatmap.h", os.path.join("..", "..", "include", "vsann.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = os.environ.get("VSANN_NVCC_FLAGS", "").split() + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
