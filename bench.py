@@ -61,6 +61,7 @@ def parse():
     p.add_argument("--no-extra", action="store_true", help="skip the i.i.d. block, the exact-mode block and the via-actor leg")
     p.add_argument("--ef", type=int, default=0, help="skip the sweep and use this ef")
     p.add_argument("--capacity-hint", type=int, default=0, help="initial reserve / growth increment per shard (0 = the shard size)")
+    p.add_argument("--one-build", action="store_true", help="profiling runs: only the host-row build (no warm-up build, no device-resident build)")
     p.add_argument("--single-process", action="store_true", help="N > 1 through ONE multi-device vs_index (vs_options.n_devices) instead of torchrun")
     return p.parse_args()
 
@@ -592,16 +593,18 @@ def main():
         torch.cuda.synchronize()
         # (1) untimed warm-up build (module load, allocator), (2) device-resident rows timed, (3) HOST rows through vs_add_batch on
         # the wall clock from the first add to count() == N - the index the searches below run on.
-        if args.warmup > 0:
+        if args.warmup > 0 and not args.one_build:
             w = new_index(hint); w.add_batch_device(keys, xd.data_ptr(), n_local); w.close()
         w = new_index(hint)
         barrier()
         t0 = time.perf_counter()
-        w.add_batch_device(keys, xd.data_ptr(), n_local)
-        assert w.count() == n_local
+        if not args.one_build:
+            w.add_batch_device(keys, xd.data_ptr(), n_local)
+            assert w.count() == n_local
         dev_wall = max_over_ranks(time.perf_counter() - t0)
         st = w.stats()
-        build["device_resident"] = {"vectors_per_s": n * S / max_over_ranks(dev_wall if G > 1 else st["build_seconds"]), "seconds_device": max_over_ranks(st["build_seconds"]),
+        if not args.one_build:
+            build["device_resident"] = {"vectors_per_s": n * S / max_over_ranks(dev_wall if G > 1 else st["build_seconds"]), "seconds_device": max_over_ranks(st["build_seconds"]),
                                     "seconds_wall": dev_wall, "rows": "already in HBM (vs_add_batch_device)"}
         w.close()
         del xd
@@ -904,15 +907,21 @@ def main():
                           f"{cpu.cores} threads; every step = the workload's {nq} queries, k={k}")
             else:
                 cpu_n = args.cpu_n or (min(n, 1_000_000) if host_gen else 200_000)
-                xs = x[:cpu_n] if host_gen else gen(cpu_n, d, 42, args.dist)
-                if not host_gen and metric_name in ("COS", "IP"):
-                    xs = xs / np.linalg.norm(xs, axis=1, keepdims=True)
+                if host_gen:
+                    xs = x[:cpu_n]
+                else:
+                    # the first cpu_n rows of THIS shard: regenerate its first chunk with the same seed and chunk size (the device generator's
+                    # values depend on the size of the draw), so that corpus and queries come from the same distribution and cluster centres
+                    first = DeviceRows(torch, dev, d, 42 + 1000 * rank, args.dist, metric_name in ("COS", "IP")).next(min(n_local, 4_000_000))
+                    xs = first[:cpu_n].cpu().numpy().copy()
+                    del first
+                    torch.cuda.empty_cache()
                 cpu = CpuIndex(vst, d, metric_name, k, cpu_n)
                 ckeys = np.arange(cpu_n, dtype=np.uint64)
                 cpu.add(ckeys, xs)
                 cq = q[:1000]
                 ctruth = numpy_truth(xs, ckeys, cq, k, metric_name)
-                sample = (f"oracle HNSW (M={M}, ef_add={EF_ADD}, AVX2 distances={cpu.simd}) on a {cpu_n}-vector SUBSAMPLE (rank 0's generator, host side) with "
+                sample = (f"oracle HNSW (M={M}, ef_add={EF_ADD}, AVX2 distances={cpu.simd}) on a {cpu_n}-vector SUBSAMPLE (the first rows of rank 0's shard) with "
                           f"{cpu.cores} threads; every step = {nq} queries, k={k}")
             log(f"CPU baseline: built {cpu.n} vectors in {cpu.build_s:.1f} s")
             ctab, cpick = cpu.sweep(cq, ctruth, grid)
