@@ -14,8 +14,10 @@ namespace vsann {
 struct WarpSmem {
     float4* q4;          // query, `chunks` float4
     SList L;             // ping-pong sorted lists
-    uint32_t* hs;        // visited hash
-    uint32_t hmask;
+    uint32_t* hs;        // visited hash: 32-bit ids, or 16-bit tags two per word (tag16)
+    uint32_t hmask;      // slots - 1
+    uint32_t hwords;     // words behind hs
+    uint32_t tag16;
     uint32_t* scr_id;    // 32
     float* scr_d;        // 32
 };
@@ -35,14 +37,18 @@ __device__ __forceinline__ WarpSmem carve_warp_smem(unsigned char* base, uint32_
     S.scr_id = reinterpret_cast<uint32_t*>(base); base += 128;
     S.scr_d = reinterpret_cast<float*>(base); base += 128;
     S.hs = reinterpret_cast<uint32_t*>(base);
-    S.hmask = hsize - 1;
+    S.hmask = hsize - 1; S.hwords = hsize; S.tag16 = 0;
     S.L.cap = cap; S.L.capp = capp;
     return S;
 }
 
 __device__ __forceinline__ void visited_clear(WarpSmem& S) {
-    for (uint32_t i = lane_id(); i <= S.hmask; i += 32) S.hs[i] = NONE;
+    const uint32_t empty = S.tag16 ? 0u : NONE;
+    for (uint32_t i = lane_id(); i < S.hwords; i += 32) S.hs[i] = empty;
     __syncwarp();
+}
+__device__ __forceinline__ bool visited_ts(uint32_t* hs, uint32_t hmask, uint32_t tag16, uint32_t id) {
+    return tag16 ? visited_test_set16(hs, hmask, id) : visited_test_set(hs, hmask, id);
 }
 
 // Greedy 1-best walk on `level` (upper levels). cur/dcur in, out.
@@ -82,7 +88,7 @@ __device__ __forceinline__ void beam_level(const GraphView& g, int level, WarpSm
         for (int off = 0; off < width; off += 32) {
             uint32_t nb = (off + (int)lane < width) ? row[off + lane] : NONE;
             if (nb != NONE && nb >= g.n_slots) nb = NONE;
-            if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+            if (nb != NONE && visited_ts(S.hs, S.hmask, S.tag16, nb)) nb = NONE;
             __syncwarp();
             float d = warp_dist32(g, S.q4, qn, nb, S.scr_id, S.scr_d, evals);
             const float worst = slist_worst(S.L);
@@ -96,7 +102,7 @@ __device__ __forceinline__ void beam_level(const GraphView& g, int level, WarpSm
 __device__ __forceinline__ void beam_seed(WarpSmem& S, uint32_t id, float d) {
     slist_init(S.L);
     visited_clear(S);
-    if (lane_id() == 0) { S.L.ld[0] = d; S.L.li[0] = id; visited_test_set(S.hs, S.hmask, id); }
+    if (lane_id() == 0) { S.L.ld[0] = d; S.L.li[0] = id; visited_ts(S.hs, S.hmask, S.tag16, id); }
     __syncwarp();
 }
 
@@ -106,7 +112,7 @@ __device__ __forceinline__ void beam_reseed_from_list(WarpSmem& S) {
     visited_clear(S);
     for (int i = lane_id(); i < S.L.cap; i += 32) {
         uint32_t id = S.L.li[i];
-        if (id != NONE) { id &= ~EXPANDED; S.L.li[i] = id; visited_test_set(S.hs, S.hmask, id); }
+        if (id != NONE) { id &= ~EXPANDED; S.L.li[i] = id; visited_ts(S.hs, S.hmask, S.tag16, id); }
     }
     __syncwarp();
 }

@@ -270,6 +270,41 @@ __device__ __forceinline__ bool visited_test_set(uint32_t* hs, uint32_t hmask, u
     return false;
 }
 
+// The same set with 16-bit TAGS, two per word (tables above 1024 slots: wide beams, where the table is most of a warp's shared
+// memory - at ef = 384 it was 16 of 20 KB and held residency to 8 warps per SM). Slot = hash(id), tag = 15 other hash bits | 1
+// (0 = empty). A foreign id with the same tag in the probe window reads as "visited" (p < 8 / 32768 per lookup: one candidate in
+// ~4000 is skipped); everything else behaves like the 32-bit table, evictions included.
+__device__ __forceinline__ bool visited_test_set16(uint32_t* hw, uint32_t smask, uint32_t id) {
+    const uint32_t h = (id * 0x9E3779B1u) >> 7, tag = ((id * 0x85EBCA6Bu) >> 16) | 1u;
+#pragma unroll 1
+    for (int probe = 0; probe < 8; ++probe) {
+        const uint32_t s = (h + probe) & smask, sh = (s & 1u) * 16u;
+        uint32_t* w = hw + (s >> 1);
+        uint32_t cur = *reinterpret_cast<volatile uint32_t*>(w);
+        for (;;) {
+            const uint32_t t = (cur >> sh) & 0xFFFFu;
+            if (t == tag) return true;
+            if (t != 0u) break;                                   // somebody else's slot: next probe
+            const uint32_t prev = atomicCAS(w, cur, cur | (tag << sh));
+            if (prev == cur) return false;
+            cur = prev;                                           // the other half of the word changed meanwhile: look again
+        }
+    }
+    const uint32_t s = h & smask, sh = (s & 1u) * 16u;            // full window: forget the entry of the home slot
+    uint32_t* w = hw + (s >> 1);
+    const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(w);
+    atomicCAS(w, cur, (cur & ~(0xFFFFu << sh)) | (tag << sh));    // best effort: losing this race only costs a re-evaluation later
+    return false;
+}
+// Which form a launch uses travels in the top bit of the `hsize` kernel argument (HASH_TAGS | slots), so that the host's
+// shared-memory arithmetic and the device's carving cannot disagree. The launcher sets it when the 32-bit table would be at
+// least as large as the warp's staging area (hash_size_for, graph_kernels.cu): measured on B200, tags buy residency there
+// (12.5M x 96: ef 384-1024 x1.4-1.6, ef 192-256 +5 %; 5M x 1536 ef 768-1024 x1.7) and cost 8 % where the staging area dominates
+// anyway (5M x 1536, ef 192-512: a tag probe is a load + a CAS where the 32-bit probe is one CAS).
+constexpr uint32_t HASH_TAGS = 0x80000000u;
+__host__ __device__ inline bool hash_uses_tags(uint32_t hsize) { return (hsize & HASH_TAGS) != 0u; }
+__host__ __device__ inline uint32_t hash_slots(uint32_t hsize) { return hsize & ~HASH_TAGS; }
+
 __device__ __forceinline__ const uint32_t* level_row(const GraphView& g, int level, uint32_t slot, int& width) {
     if (level == 0) { width = g.W0; return g.links0 + (size_t)slot * g.W0; }
     width = g.M;

@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
 // Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
 // float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
 template <int NL, int CPL>
-__global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : 2)) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
+__global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : (NL <= 16 ? 4 : 3))) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                      uint32_t ef, uint32_t hsize, uint32_t stage_rows,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
                                                      unsigned long long* counters, uint32_t* work) {
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(256) k_search_blk(const __grid_constant__ CUte
                     int width; const uint32_t* row = level_row(g, 0, c, width);
                     nb = ((int)lane < width) ? row[lane] : NONE;
                     if (nb != NONE && nb >= g.n_slots) nb = NONE;
-                    if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+                    if (nb != NONE && visited_ts(S.hs, S.hmask, S.tag16, nb)) nb = NONE;
                     __syncwarp();
                 }
             }
@@ -798,17 +798,20 @@ static inline int vecs_tmap(const GraphView& g, const DeviceInfo& dev, CUtensorM
     if (!dev.gather4 || g.dpad > 256 || (g.dpad & 7u) || g.n_slots == 0) return 0;   // groups of 4 rows must stay 128 B aligned
     return make_tmap_f32(m, g.vecs, g.n_slots, g.dpad, g.dpad, g.dpad, 1, CU_TENSOR_MAP_SWIZZLE_NONE) ? 1 : 0;
 }
-static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev) {
+static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev, const GraphView& g, uint32_t stage_rows) {
     uint32_t hs = next_pow2(ef * dev.hash_factor);
     if (hs < dev.hash_min) hs = dev.hash_min;
     if (hs > 16384) hs = 16384;
-    return hs;
+    // 16-bit tags where the table would otherwise be the larger part of the warp's shared memory (common.cuh HASH_TAGS)
+    static const int force = [] { const char* e = getenv("VSANN_HASH_TAGS"); return e ? atoi(e) : -1; }();   // A/B: 0 never, 1 whenever > 1024 slots
+    const bool tags = hs > 1024 && (force == 1 || (force != 0 && (size_t)hs * 4 >= (size_t)stage_rows * g.dpad * 4));
+    return tags ? (hs | HASH_TAGS) : hs;
 }
 
 template <int NL, int CPL>
 static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
-    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev);
+    const uint32_t rows = stage_rows_for(g, dev), hs = hash_size_for(ef, dev, g, rows);
     uint32_t wpb = 4;
     // wide lists (ef > 256: NL = 16 / 32 list registers per lane) with long rows: fewer warps per block so that hash + staging fit
     while (NL > 8 && wpb > 1 && tsmem_bytes(g.dpad, hs, rows) * wpb > dev.smem_per_block) wpb >>= 1;
@@ -834,7 +837,7 @@ static cudaError_t launch_search_tc(const GraphView& g, const float* d_queries, 
 template <int NL, int CPL>
 static cudaError_t launch_build_search_t(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
                                          unsigned long long* counters, cudaStream_t st) {
-    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev), wpb = 4;
+    const uint32_t rows = stage_rows_for(g, dev), hs = hash_size_for(ef, dev, g, rows), wpb = 4;
     const size_t smem = tsmem_bytes(g.dpad, hs, rows) * wpb;
     if (smem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_build_search_t<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -872,7 +875,7 @@ static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, u
 template <int NL, int CPL>
 static cudaError_t launch_search_blk_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
                                        uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
-    const uint32_t hs = hash_size_for(ef, dev), rows = stage_rows_for(g, dev);
+    const uint32_t rows = stage_rows_for(g, dev), hs = hash_size_for(ef, dev, g, rows);
     const size_t per_warp = tsmem_bytes(g.dpad, hs, rows);
     uint32_t W = 8;
     while (W > 1 && per_warp * W + 1024 > dev.smem_per_block) --W;

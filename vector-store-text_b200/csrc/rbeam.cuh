@@ -121,7 +121,7 @@ struct SortedList {
 
     __device__ __forceinline__ void reopen_all(WarpSmem& S) {
 #pragma unroll
-        for (int j = 0; j < NL; ++j) if (id[j] != NONE) { id[j] &= ~EXPANDED; visited_test_set(S.hs, S.hmask, id[j]); }
+        for (int j = 0; j < NL; ++j) if (id[j] != NONE) { id[j] &= ~EXPANDED; visited_ts(S.hs, S.hmask, S.tag16, id[j]); }
     }
 
     // First unexpanded entry; marks it expanded. NONE when the beam is finished.
@@ -225,7 +225,7 @@ struct UList {
     __device__ __forceinline__ void seed(float nd, uint32_t nid) { insert(nd, nid); }
     __device__ __forceinline__ void reopen_all(WarpSmem& S) {
 #pragma unroll
-        for (int j = 0; j < NL; ++j) if (id[j] != NONE) { id[j] &= ~EXPANDED; visited_test_set(S.hs, S.hmask, id[j] & ID_MASK); }
+        for (int j = 0; j < NL; ++j) if (id[j] != NONE) { id[j] &= ~EXPANDED; visited_ts(S.hs, S.hmask, S.tag16, id[j] & ID_MASK); }
     }
     __device__ __forceinline__ uint32_t pop(float& d_out) { return nearest_open(d_out, true); }
     __device__ __forceinline__ uint32_t peek() { float d; return nearest_open(d, false); }
@@ -305,7 +305,7 @@ __device__ __forceinline__ void rbeam_level(const GraphView& g, int level, WarpS
         for (int off = 0; off < width; off += 32) {
             uint32_t nb = (off + (int)lane < width) ? row[off + lane] : NONE;
             if (nb != NONE && nb >= g.n_slots) nb = NONE;
-            if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+            if (nb != NONE && visited_ts(S.hs, S.hmask, S.tag16, nb)) nb = NONE;
             __syncwarp();
             const float d = warp_dist32(g, S.q4, qn, nb, S.scr_id, S.scr_d, evals);
             unsigned acc = __ballot_sync(0xffffffffu, nb != NONE && d < L.worst);
@@ -323,7 +323,7 @@ template <class LIST>
 __device__ __forceinline__ void rbeam_seed(WarpSmem& S, LIST& L, int cap, uint32_t id, float d) {
     L.init(cap);
     visited_clear(S);
-    if (lane_id() == 0) visited_test_set(S.hs, S.hmask, id);
+    if (lane_id() == 0) visited_ts(S.hs, S.hmask, S.tag16, id);
     __syncwarp();
     L.seed(d, id);
 }

@@ -90,7 +90,7 @@ struct WarpStage {
 
 // per-warp layout: query | scr_id[32] | scr_d[32] | 8 mbarriers (one per staging slot of four rows) | visited hash | staging rows (128 B aligned)
 __host__ __device__ inline size_t tsmem_bytes(uint32_t dpad, uint32_t hsize, uint32_t rows) {
-    size_t b = (size_t)dpad * 4 + 256 + 64 + (size_t)hsize * 4;
+    size_t b = (size_t)dpad * 4 + 256 + 64 + (size_t)hash_slots(hsize) * (hash_uses_tags(hsize) ? 2 : 4);
     b = (b + 127) & ~(size_t)127;
     return b + (size_t)rows * dpad * 4;
 }
@@ -101,8 +101,9 @@ __device__ __forceinline__ void carve_tsmem(unsigned char* base, uint32_t dpad, 
     S.scr_id = reinterpret_cast<uint32_t*>(p); p += 128;
     S.scr_d = reinterpret_cast<float*>(p); p += 128;
     T.bar = smem_u32(p); p += 64;
-    S.hs = reinterpret_cast<uint32_t*>(p); p += (size_t)hsize * 4;
-    S.hmask = hsize - 1;
+    S.tag16 = hash_uses_tags(hsize) ? 1u : 0u; S.hwords = S.tag16 ? hash_slots(hsize) / 2 : hash_slots(hsize);
+    S.hs = reinterpret_cast<uint32_t*>(p); p += (size_t)S.hwords * 4;
+    S.hmask = hash_slots(hsize) - 1;
     p = base + ((((size_t)(p - base)) + 127) & ~(size_t)127);
     T.buf = p; T.buf_s = smem_u32(p);
     T.rows = rows; T.row_bytes = dpad * 4; T.parity = 0; T.tmap = nullptr; T.pf_over = false;
@@ -149,7 +150,7 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
     const unsigned lane = lane_id(), team = lane >> 3, tl = lane & 7u;
     const unsigned valid = __ballot_sync(0xffffffffu, id != NONE);
     if (valid == 0u) {
-        if (pf != NONE && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
+        if (pf != NONE && !S.tag16 && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
         return INFINITY;
     }
     const int nvalid = __popc(valid);
@@ -166,7 +167,7 @@ __device__ __forceinline__ float stage_dist32_m(const GraphView& g, WarpSmem& S,
     // Measured on B200: search 15.15M -> 15.73M QPS; the build search (ef_add wide, mostly L2-resident) loses 2 %, so it is per kernel.
     if (T.pf_over && (int)lane >= (int)T.rows && (int)lane < nvalid) bulk_prefetch_l2(g.vecs + (size_t)S.scr_id[lane] * g.dpad, T.row_bytes);
     // while this expansion's rows are in flight: bring the not yet visited neighbours of the likely next node into L2
-    if (pf != NONE && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
+    if (pf != NONE && !S.tag16 && pf < g.n_slots && !visited_probe(S.hs, S.hmask, pf)) bulk_prefetch_l2(g.vecs + (size_t)pf * g.dpad, T.row_bytes);
     if (METRIC == COS) { if (id != NONE) S.scr_d[pos] = g.sqn[id]; __syncwarp(); }
     int slot = 0;
     for (int grp = 0; grp < ngroups; ++grp) {
@@ -263,7 +264,7 @@ __device__ __forceinline__ void tbeam_level(const GraphView& g, int level, WarpS
         {
             uint32_t nb = nb_row;
             if (nb != NONE && nb >= g.n_slots) nb = NONE;
-            if (nb != NONE && visited_test_set(S.hs, S.hmask, nb)) nb = NONE;
+            if (nb != NONE && visited_ts(S.hs, S.hmask, S.tag16, nb)) nb = NONE;
             __syncwarp();
             const float d = stage_dist32<CPL>(g, S, T, Q, qn, nb, evals, PF_NEXT && spec_id != NONE ? spec_nb : NONE);
             const bool good = nb != NONE && d < L.worst;
