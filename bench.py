@@ -281,8 +281,9 @@ def numpy_truth(x, keys, q, k, metric):
     enough to rank neighbours for a recall figure (it is NOT the bit-exact oracle definition)."""
     out = np.empty((q.shape[0], k), dtype=np.uint64)
     xn = (x * x).sum(1) if metric == "L2SQ" else None
-    for a in range(0, q.shape[0], 256):
-        s = q[a:a + 256] @ x.T
+    step = int(max(8, min(256, (1 << 28) // max(1, x.shape[0]))))     # <= 1 GiB of scores per block of queries
+    for a in range(0, q.shape[0], step):
+        s = q[a:a + step] @ x.T
         if metric == "L2SQ":
             s = xn[None, :] - 2.0 * s
         elif metric == "COS":
@@ -292,7 +293,7 @@ def numpy_truth(x, keys, q, k, metric):
         idx = np.argpartition(s, k, axis=1)[:, :k]
         part = np.take_along_axis(s, idx, 1)
         order = np.argsort(part, axis=1)
-        out[a:a + 256] = keys[np.take_along_axis(idx, order, 1)]
+        out[a:a + step] = keys[np.take_along_axis(idx, order, 1)]
     return out
 
 
@@ -391,7 +392,8 @@ def run_reference(args):
     nq = args.nq or cfg["nq"]
     n_shard = shard_size(args, cfg, world)
     total = n_shard * world
-    cpu_n = args.cpu_n or (total if cfg["gen"] == "host" else min(total, 200_000))
+    # configs[1]: the whole corpus up to 4M vectors (N <= 4 shards); beyond that a stated 4M-vector part, so that the arm still ends within minutes
+    cpu_n = args.cpu_n or (min(total, 4_000_000) if cfg["gen"] == "host" else min(total, 200_000))
     cpu = CpuIndex(vst, d, metric, k, cpu_n)
     xs, ks = [], []
     if cfg["gen"] == "host":
@@ -418,7 +420,7 @@ def run_reference(args):
         sample = (f"oracle HNSW (M={M}, ef_add={EF_ADD}, AVX2 distances={cpu.simd}) on a {cpu_n}-vector SUBSAMPLE of the workload's distribution "
                   f"({total} vectors would take hours on the host), {cpu.cores} threads; every step = {nq} queries, k={k}")
     xa, ka = np.concatenate(xs), np.concatenate(ks)
-    ts_n = min(1000, nq)
+    ts_n = min(1000 if len(xa) <= 2_000_000 else 200, nq)
     truth = numpy_truth(xa, ka, q[:ts_n], k, metric)
     tab, pick = cpu.sweep(q[:ts_n], truth, [args.ef] if args.ef else EF_GRID[k])
     reached = pick is not None
