@@ -17,8 +17,13 @@
 // tombstoned rows and rows past the end get (0, +inf). dist = f(key) is monotone per query.
 //
 // CTA = 128 queries (UMMA M) x one corpus slice, tiles of 256 rows (UMMA N), K in blocks of 32 floats
-// (one 128 B swizzle row). Warps 0-7: epilogue (TMEM lane quarter = warp % 4, column half = warp / 4), warp 8: TMA
-// producer, warp 9: MMA issuer + TMEM allocator, warp 10: per-row coefficients. 4-stage smem ring, 2 TMEM accumulators of 256 columns.
+// (one 128 B swizzle row). Warps 0..E-1: epilogue (TMEM lane quarter = warp % 4, column part = warp / 4; E = 8 sampling, 16 full scan),
+// warp E: TMA producer, warp E+1: MMA issuer + TMEM allocator, warp E+2: per-row coefficients. 4-stage smem ring, 2 TMEM accumulators of 256 columns.
+// Queries of up to 128 dimensions (4 K blocks) stay RESIDENT in shared memory for the CTA's lifetime: the ring then carries corpus
+// tiles only and the L2 -> SM traffic per tile drops from 192 KB to 128 KB (the scan ran at the L2's delivery rate: 62 GB per
+// 10k x 1M x 128 scan = 12.1 TB/s, profiles/r02m). The coefficient warp runs up to 8 tiles ahead of the epilogue through its own
+// ring (it waited for the epilogue to free one of two buffers and then for its global loads: 15 % of the epilogue's samples), and
+// the epilogue never waits for an atomic: the ids of a chunk are written when the next chunk with candidates comes by.
 #include <cuda.h>
 #include <algorithm>
 #include <cmath>
@@ -33,21 +38,26 @@ namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 32, STAGES = 4, UMMA_K = 8;
 constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4, STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int EPI_WARPS = 8, EPI_THREADS = EPI_WARPS * 32, THREADS = EPI_THREADS + 96;   // + TMA, MMA, coefficient warps
-constexpr int W_TMA = EPI_WARPS, W_MMA = EPI_WARPS + 1, W_COEF = EPI_WARPS + 2;
-constexpr int EPI_COLS = BN / (EPI_WARPS / 4);   // columns one epilogue warp scans per tile
+// epilogue warps: 8 in the sampling pass (a thread keeps R_MAX keys in registers), 16 in the full scan - its epilogue is a chain of
+// TMEM loads, shared-memory loads and dependent minima, bound by latency, not issue slots (36 % busy with 8 warps: profiles/r02m)
+constexpr int EPI_WARPS = 8, EPI_WARPS_EMIT = 16;
+__host__ __device__ constexpr int epi_warps(bool emit) { return emit ? EPI_WARPS_EMIT : EPI_WARPS; }
+__host__ __device__ constexpr int threads_of(bool emit) { return epi_warps(emit) * 32 + 96; }   // + TMA, MMA, coefficient warps
 constexpr int R_MAX = 16;              // sampled keys kept per (query, slice)
 constexpr int SAMPLE_STRIDE = 32;      // large corpora: every 32nd tile is sampled (small ones: Plan::stride)
 constexpr uint32_t TMEM_COLS = 512;
+constexpr int CB = 8, CG = 4;           // coefficient ring: buffers, tiles whose loads one round of the coefficient warp has in flight
+constexpr int RES_KB = 4;              // query K blocks that stay resident (d <= 128)
 constexpr uint32_t R2_MAX = 1024;      // queries the second (proven-threshold) scan serves at most; more than that go to the FP32 fallback
 
 // dynamic shared memory (after rounding the base up to 1024 B)
 struct __align__(16) Ctrl {
-    unsigned long long full[STAGES], empty[STAGES], tfull[2], tempty[2], cfull[2];
+    unsigned long long full[STAGES], empty[STAGES], tfull[2], tempty[2], cfull[CB], cempty[CB], afull;
     uint32_t tmem_base;
-    uint32_t pad[3];
+    uint32_t pad[1];
 };
-constexpr size_t COLV_BYTES = 2 * BN * sizeof(float2);
+constexpr size_t COLV_BYTES = (size_t)CB * BN * sizeof(float2);
+static_assert((size_t)RES_KB * A_BYTES + (size_t)STAGES * B_BYTES <= (size_t)STAGES * STAGE_BYTES, "resident layout fits the streaming one");
 constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + COLV_BYTES + sizeof(Ctrl);
 
 // ---- PTX wrappers --------------------------------------------------------------------------
@@ -122,21 +132,37 @@ struct ScanArgs {
     float* samp;                                 // SAMPLE: [slices * EPI_WARPS / 4][nq_pad][R_MAX] ascending
     const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
     const uint32_t* n_active; uint32_t active_cap;                    // second scan: the query count lives on the device (null = nq)
+    uint32_t flags;                                                   // A/B switches (VSANN_TC_FLAGS): 1 = queries not resident, 2 = coefficient loads one tile at a time, 4 = ids written at once
 };
 
-// (a, b) of one corpus row: key = a * dot + b
-__device__ __forceinline__ float2 row_coeffs(const ScanArgs& a, uint32_t r) {
-    if (r >= a.n) return make_float2(0.f, INFINITY);
+// (a, b) of one corpus row: key = a * dot + b. In two halves, so that the coefficient warp can issue the loads of several tiles
+// back to back and look at the values afterwards: written as one function with early returns, every row cost two DEPENDENT
+// round trips to an L2 that is busy delivering 12 TB/s of tiles (16 in a row per tile, 2.4 us: that, not the tensor pipe or the
+// epilogue's arithmetic, set the pace of the scan - profiles/r02m).
+struct RowRaw { uint32_t bits; float xn; };
+__device__ __forceinline__ RowRaw row_load(const ScanArgs& a, uint32_t r) {
+    const uint32_t rr = min(r, a.n - 1u), slot = a.first_slot + rr;
+    const uint32_t* del = a.deleted ? a.deleted : reinterpret_cast<const uint32_t*>(a.sqn);     // no tombstones: any readable word
+    RowRaw x;
+    x.bits = __ldg(del + (a.deleted ? (slot >> 5) : 0u));
+    x.xn = __ldg(a.sqn + rr);
+    return x;
+}
+__device__ __forceinline__ float2 row_coeffs(const ScanArgs& a, uint32_t r, const RowRaw x) {
     const uint32_t slot = a.first_slot + r;
-    if (a.deleted && ((a.deleted[slot >> 5] >> (slot & 31u)) & 1u)) return make_float2(0.f, INFINITY);
-    if (a.metric == L2SQ) return make_float2(-2.f, a.sqn[r]);
-    if (a.metric == IP) return make_float2(-1.f, 0.f);
-    const float xn = a.sqn[r];
-    return make_float2(xn > 0.f ? -rsqrtf(xn) : 0.f, 0.f);
+    const bool dead = a.deleted != nullptr && ((x.bits >> (slot & 31u)) & 1u);
+    float2 ab;
+    if (a.metric == L2SQ) ab = make_float2(-2.f, x.xn);
+    else if (a.metric == IP) ab = make_float2(-1.f, 0.f);
+    else ab = make_float2(x.xn > 0.f ? -rsqrtf(x.xn) : 0.f, 0.f);
+    if (r >= a.n || dead) ab = make_float2(0.f, INFINITY);
+    return ab;
 }
 
-template <bool EMIT>
-__global__ void __launch_bounds__(THREADS, 1)
+// R: sampled keys a thread keeps (sampling pass only): the insertion network costs 2 (R - 1) instructions per accepted key, and a
+// key accepted by ONE of a warp's 32 queries is paid for by all of them
+template <bool EMIT, int R>
+__global__ void __launch_bounds__(threads_of(EMIT), 1)
 k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapX, const ScanArgs a) {
     extern __shared__ unsigned char smem_raw[];
     // round the base up to 1024 B (128 B swizzle atoms) by pointer arithmetic, so the compiler keeps the shared address space
@@ -144,6 +170,12 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     float2* colv = reinterpret_cast<float2*>(smem + (size_t)STAGES * STAGE_BYTES);
     Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem + (size_t)STAGES * STAGE_BYTES + COLV_BYTES);
     const uint32_t smem_s = s32(smem);
+    // resident query tile: K blocks 0..kblocks-1 at the front, the ring (corpus tiles only) behind them; otherwise a stage = (A, B)
+    const bool res_a = a.kblocks <= (uint32_t)RES_KB && !(a.flags & 1u);
+    const uint32_t ring_s = smem_s + (res_a ? (uint32_t)(RES_KB * A_BYTES) : 0u), stage_bytes = res_a ? (uint32_t)B_BYTES : (uint32_t)STAGE_BYTES,
+                   b_off = res_a ? 0u : (uint32_t)A_BYTES;
+    constexpr int EW = epi_warps(EMIT), W_TMA = EW, W_MMA = EW + 1, W_COEF = EW + 2;
+    constexpr int EPI_COLS = BN / (EW / 4);   // columns one epilogue warp scans per tile
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t q0 = blockIdx.x * BM, slice = blockIdx.y;
     // second scan: launched for the largest query count it may see; CTAs past the count the first round left on the device leave at once
@@ -155,7 +187,9 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), EPI_WARPS); mbar_init(s32(&ctrl->cfull[i]), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), EW); }
+        for (int i = 0; i < CB; ++i) { mbar_init(s32(&ctrl->cfull[i]), 1); mbar_init(s32(&ctrl->cempty[i]), EW); }
+        mbar_init(s32(&ctrl->afull), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == W_MMA) {
@@ -171,14 +205,18 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
+            if (res_a && t_first < t_end) {
+                mbar_expect_tx(s32(&ctrl->afull), a.kblocks * A_BYTES);
+                for (uint32_t kb = 0; kb < a.kblocks; ++kb) tma_load_2d(smem_s + kb * A_BYTES, &mapQ, s32(&ctrl->afull), (int)(kb * BK), (int)q0);
+            }
             for (uint32_t t = t_first; t < t_end; t += t_step) {
                 for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
                     mbar_wait(s32(&ctrl->empty[stage]), phase ^ 1u);
                     const uint32_t full = s32(&ctrl->full[stage]);
-                    mbar_expect_tx(full, STAGE_BYTES);
-                    const uint32_t dst = smem_s + stage * STAGE_BYTES;
-                    tma_load_2d(dst, &mapQ, full, (int)(kb * BK), (int)q0);
-                    tma_load_2d(dst + A_BYTES, &mapX, full, (int)(kb * BK), (int)(t * BN));
+                    mbar_expect_tx(full, res_a ? B_BYTES : STAGE_BYTES);
+                    const uint32_t dst = ring_s + stage * stage_bytes;
+                    if (!res_a) tma_load_2d(dst, &mapQ, full, (int)(kb * BK), (int)q0);
+                    tma_load_2d(dst + b_off, &mapX, full, (int)(kb * BK), (int)(t * BN));
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -187,6 +225,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0, it = 0;
+            if (res_a && t_first < t_end) mbar_wait(s32(&ctrl->afull), 0u);
             for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
                 const uint32_t buf = it & 1u;
                 mbar_wait(s32(&ctrl->tempty[buf]), ((it >> 1) & 1u) ^ 1u);
@@ -195,8 +234,8 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                 for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
                     mbar_wait(s32(&ctrl->full[stage]), phase);
                     tc_fence_after();
-                    const uint64_t da = smem_desc_sw128(smem_s + stage * STAGE_BYTES);
-                    const uint64_t db = smem_desc_sw128(smem_s + stage * STAGE_BYTES + A_BYTES);
+                    const uint64_t da = smem_desc_sw128(res_a ? smem_s + kb * A_BYTES : ring_s + stage * stage_bytes);
+                    const uint64_t db = smem_desc_sw128(ring_s + stage * stage_bytes + b_off);
 #ifndef TC_DEBUG_SKIP_MMA
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
@@ -211,18 +250,30 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
             }
         }
     } else if (warp == W_COEF) {
-        // ===== row coefficients (a_j, b_j) of the tile, one buffer per accumulator buffer =====
+        // ===== row coefficients (a_j, b_j) of the tiles, through a ring of CB buffers: the global loads of CG tiles are in flight
+        // together, and the warp runs ahead of the epilogue by up to CB tiles =====
         uint32_t it = 0;
-        for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
-            const uint32_t buf = it & 1u;
-            mbar_wait(s32(&ctrl->tempty[buf]), ((it >> 1) & 1u) ^ 1u);      // the epilogue is done with colv[buf]
-            float2 ab[BN / 32];
+        const int cg = (a.flags & 2u) ? 1 : CG;
+        for (uint32_t t = t_first; t < t_end; t += cg * t_step) {
+            RowRaw raw[CG][BN / 32];
 #pragma unroll
-            for (int j = 0; j < BN / 32; ++j) ab[j] = row_coeffs(a, t * BN + j * 32 + lane);
+            for (int gi = 0; gi < CG; ++gi) {
+                const uint32_t tg = min(t + (gi < cg ? gi : 0) * t_step, t_end - 1u);      // (rounds past the end re-read a valid tile and drop it)
 #pragma unroll
-            for (int j = 0; j < BN / 32; ++j) colv[buf * BN + j * 32 + lane] = ab[j];
-            __syncwarp();
-            if (lane == 0) mbar_arrive(s32(&ctrl->cfull[buf]));
+                for (int j = 0; j < BN / 32; ++j) raw[gi][j] = row_load(a, tg * BN + j * 32 + lane);
+            }
+#pragma unroll
+            for (int gi = 0; gi < CG; ++gi) {
+                if (t + gi * t_step < t_end && gi < cg) {
+                    const uint32_t cb = it & (CB - 1);
+                    mbar_wait(s32(&ctrl->cempty[cb]), ((it / CB) & 1u) ^ 1u);       // the epilogue is done with colv[cb]
+#pragma unroll
+                    for (int j = 0; j < BN / 32; ++j) colv[cb * BN + j * 32 + lane] = row_coeffs(a, (t + gi * t_step) * BN + j * 32 + lane, raw[gi][j]);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(s32(&ctrl->cfull[cb]));
+                    ++it;
+                }
+            }
         }
     } else {
         // ===== epilogue: thread = one query row of the accumulator =====
@@ -231,44 +282,77 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
         const bool qok = q < nq_eff;
         float tau = -INFINITY;
         if (EMIT && qok) tau = a.tau[q];
-        float top[R_MAX];
+        float top[R];
 #pragma unroll
-        for (int i = 0; i < R_MAX; ++i) top[i] = INFINITY;
+        for (int i = 0; i < R; ++i) top[i] = INFINITY;
+        uint32_t pend_hits = 0, pend_pos = 0, pend_base = 0;
+        auto flush_pending = [&]() {
+            while (pend_hits) {
+                const uint32_t i = (uint32_t)__ffs(pend_hits) - 1u; pend_hits &= pend_hits - 1u;
+                if (pend_pos < a.cap) a.cand[(size_t)q * a.cap + pend_pos] = pend_base + i;
+                ++pend_pos;
+            }
+        };
         uint32_t it = 0;
         for (uint32_t t = t_first; t < t_end; t += t_step, ++it) {
-            const uint32_t buf = it & 1u;
-            mbar_wait(s32(&ctrl->cfull[buf]), (it >> 1) & 1u);
+            const uint32_t buf = it & 1u, cb = it & (CB - 1);
+            mbar_wait(s32(&ctrl->cfull[cb]), (it / CB) & 1u);
             mbar_wait(s32(&ctrl->tfull[buf]), (it >> 1) & 1u);
             tc_fence_after();
-            const float2* cv = colv + buf * BN + half * EPI_COLS;
+            const float2* cv = colv + cb * BN + half * EPI_COLS;
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + buf * BN + half * EPI_COLS;
-            // Hot loop: key = a * dot + b and a running minimum, branch-free; the (rare) chunks whose minimum passes
-            // the bound are re-scanned element by element. The next 32 columns are in flight while these are processed.
+            // Hot loop: key = a * dot + b and running minima over groups of 8 columns, branch-free; the (rare) groups whose minimum
+            // passes the bound are re-scanned element by element. The next 32 columns are in flight while these are processed.
             const float4* cv4 = reinterpret_cast<const float4*>(cv);
             auto process = [&](const float (&v)[32], int c) {
-                float mn = INFINITY;
+                float m[4];
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    const float4 ab = cv4[(c * 32 + i) >> 1];
-                    mn = fminf(mn, fminf(fmaf(ab.x, v[i], ab.y), fmaf(ab.z, v[i + 1], ab.w)));
+                for (int g = 0; g < 4; ++g) {
+                    float mg = INFINITY;
+#pragma unroll
+                    for (int i = g * 8; i < g * 8 + 8; i += 2) {
+                        const float4 ab = cv4[(c * 32 + i) >> 1];
+                        mg = fminf(mg, fminf(fmaf(ab.x, v[i], ab.y), fmaf(ab.z, v[i + 1], ab.w)));
+                    }
+                    m[g] = mg;
                 }
-                const float bound = EMIT ? tau : top[R_MAX - 1];
-                if (EMIT ? (mn <= bound) : (mn < bound)) {
+                const float mn = fminf(fminf(m[0], m[1]), fminf(m[2], m[3]));
+                if (EMIT) {
+                    if (mn <= tau) {
+                        uint32_t hits = 0;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {   // unrolled: v[] stays in registers
-                        const float2 ab = cv[c * 32 + i];
-                        const float key = fmaf(ab.x, v[i], ab.y);
-                        if (EMIT) {
-                            if (key <= tau) {
-                                const uint32_t pos = atomicAdd(&a.cnt[q], 1u);
-                                if (pos < a.cap) a.cand[(size_t)q * a.cap + pos] = a.first_slot + t * BN + half * EPI_COLS + c * 32 + i;
+                        for (int g = 0; g < 4; ++g) {
+                            if (m[g] <= tau) {
+#pragma unroll
+                                for (int i = g * 8; i < g * 8 + 8; ++i) {   // unrolled: v[] stays in registers
+                                    const float2 ab = cv[c * 32 + i];
+                                    if (fmaf(ab.x, v[i], ab.y) <= tau) hits |= 1u << i;
+                                }
                             }
-                        } else if (key < top[R_MAX - 1]) {
-                            top[R_MAX - 1] = key;
+                        }
+                        // one atomic per chunk with candidates, and nobody waits for it: the ids are written when the next such
+                        // chunk comes by (or at the end), long after the position has come back
+                        flush_pending();
+                        pend_pos = atomicAdd(&a.cnt[q], (uint32_t)__popc(hits));
+                        pend_hits = hits; pend_base = a.first_slot + t * BN + half * EPI_COLS + c * 32;
+                        if (a.flags & 4u) flush_pending();
+                    }
+                } else if (mn < top[R - 1]) {
 #pragma unroll
-                            for (int j = R_MAX - 1; j > 0; --j) {
-                                const float lo = fminf(top[j - 1], top[j]), hi = fmaxf(top[j - 1], top[j]);
-                                top[j - 1] = lo; top[j] = hi;
+                    for (int g = 0; g < 4; ++g) {
+                        if (m[g] < top[R - 1]) {
+#pragma unroll
+                            for (int i = g * 8; i < g * 8 + 8; ++i) {
+                                const float2 ab = cv[c * 32 + i];
+                                const float key = fmaf(ab.x, v[i], ab.y);
+                                if (key < top[R - 1]) {
+                                    top[R - 1] = key;
+#pragma unroll
+                                    for (int j = R - 1; j > 0; --j) {
+                                        const float lo = fminf(top[j - 1], top[j]), hi = fmaxf(top[j - 1], top[j]);
+                                        top[j - 1] = lo; top[j] = hi;
+                                    }
+                                }
                             }
                         }
                     }
@@ -289,12 +373,13 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
 #endif
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(s32(&ctrl->tempty[buf]));
+            if (lane == 0) { mbar_arrive(s32(&ctrl->tempty[buf])); mbar_arrive(s32(&ctrl->cempty[cb])); }
         }
+        if (EMIT) flush_pending();
         if (!EMIT && qok) {
             float* o = a.samp + ((size_t)(slice * (EPI_WARPS / 4) + half) * a.nq_pad + q) * R_MAX;
 #pragma unroll
-            for (int i = 0; i < R_MAX; ++i) o[i] = top[i];
+            for (int i = 0; i < R_MAX; ++i) o[i] = i < R ? top[i] : INFINITY;
         }
     }
     tc_fence_before();
@@ -592,12 +677,24 @@ static bool make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t 
     return make_tmap_f32(m, base, rows, dpad, row_stride_floats, BK, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
-struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, kblocks, stride, r, cap, kp; bool ok; };
+struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, s_slices, s_tiles_per_slice, kblocks, stride, r, cap, kp; bool ok; };
 
 // r-th smallest of a 1/stride sample as threshold: expected stride * r rows pass, P(fewer than k pass) < 1e-3
 static uint32_t sample_rank(uint32_t k, uint32_t stride) {
     const float lam = (float)k / stride;
     return (uint32_t)std::ceil(lam + 4.f * std::sqrt(lam) + 3.5f);
+}
+
+// Slices per query tile in [lo, hi] whose grid fills its last wave best (one CTA per SM, CTAs of equal length): 79 query tiles x 15
+// slices = 148 x 8 + 1 CTAs ran a ninth wave for a single CTA (11 % of the scan). Ties go to the finer slicing.
+static uint32_t pick_slices(uint32_t nqt, uint32_t lo, uint32_t hi, int sm_count) {
+    uint32_t best = hi; double best_eff = -1.0;
+    for (uint32_t s = hi; s >= lo && s >= 1; --s) {
+        const double waves = (double)nqt * s / sm_count, eff = waves / std::ceil(waves);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+        if (s == 1) break;
+    }
+    return best;
 }
 
 static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
@@ -609,6 +706,7 @@ static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm
     want = std::min<uint32_t>(want, std::max<uint32_t>(1u, p.n_tiles / 8));   // >= 8 tiles per CTA
     // (a cap of 64 slices left 64 of 148 SMs busy for a single query tile: 2.3 TB/s at 5M x 1536, B <= 128)
     want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 1024u));
+    want = pick_slices(p.nqt, std::max<uint32_t>(1u, (want + 1) / 2), want, sm_count);
     p.tiles_per_slice = std::max<uint32_t>(1u, (p.n_tiles + want - 1) / want);
     p.slices = (p.n_tiles + p.tiles_per_slice - 1) / p.tiles_per_slice;
     // sampling stride: 32 on large corpora (the sample pass is the slow one per tile), denser on small ones so
@@ -617,6 +715,14 @@ static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm
     p.stride = p.n_tiles >= 512 ? SAMPLE_STRIDE : std::min<uint32_t>(SAMPLE_STRIDE, std::max<uint32_t>(smin, p.n_tiles / 16));
     p.ok = sample_rank(k, p.stride) <= R_MAX && p.n_tiles >= 2 * p.stride;
     p.r = std::min<uint32_t>(R_MAX, sample_rank(k, p.stride));
+    // The sampling pass has its own, coarser slicing (~2 waves of CTAs, at least one sampled tile each): a thread that sees more
+    // keys accepts a smaller share of them (R ln(m / R) of m), and with 8 tiles per CTA 85 % of the sampled keys went through
+    // the insertion network of all 32 lanes (0.67 ms for 1/32 of the work of the 3.8 ms full scan)
+    uint32_t want_s = (2u * (uint32_t)sm_count + p.nqt - 1) / p.nqt;
+    const uint32_t cap_s = std::max<uint32_t>(1u, std::min<uint32_t>(p.slices, std::max<uint32_t>(1u, p.n_tiles / p.stride)));
+    want_s = pick_slices(p.nqt, std::max<uint32_t>(1u, std::min<uint32_t>(cap_s, (want_s + 1) / 2)), std::max<uint32_t>(1u, std::min<uint32_t>(cap_s, 2 * want_s)), sm_count);
+    p.s_tiles_per_slice = std::max<uint32_t>(1u, (p.n_tiles + want_s - 1) / want_s);
+    p.s_slices = (p.n_tiles + p.s_tiles_per_slice - 1) / p.s_tiles_per_slice;
     uint32_t cap = 1; while (cap < (k >= 32 ? 8u : 4u) * p.r * p.stride) cap <<= 1;   // k >= 32: room for a widened threshold in dense data
     p.cap = cap;
     p.kp = (k + 31u) & ~31u;
@@ -648,7 +754,7 @@ static size_t carve(const Plan& p, uint32_t nq, uint32_t dpad, unsigned char* ba
     auto take = [&](size_t bytes) { unsigned char* r = base ? base + off : nullptr; off += al256(bytes); return r; };
     Scratch t{};
     t.qn = (float*)take((size_t)nq * 4); t.tau = (float*)take((size_t)nq * 4); t.cnt = (uint32_t*)take((size_t)nq * 4);
-    t.samp = (float*)take((size_t)p.slices * (EPI_WARPS / 4) * p.nq_pad * R_MAX * 4);
+    t.samp = (float*)take((size_t)p.s_slices * (EPI_WARPS / 4) * p.nq_pad * R_MAX * 4);
     t.cand = (uint32_t*)take((size_t)nq * p.cap * 4); t.cand_d = (float*)take((size_t)nq * p.cap * 4);
     t.ctr = (uint32_t*)take(16);
     t.r2_ids = (uint32_t*)take((size_t)nq * 4); t.r2_tau = (float*)take((size_t)nq * 4); t.r2_qn = (float*)take((size_t)nq * 4);
@@ -679,8 +785,9 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     if (!make_map(&mapQ, q.q, q.nq, q.dpad, q.stride, BM) || !make_map(&mapX, c.vecs, c.n, q.dpad, c.row_stride, BN)) return cudaErrorNotSupported;
     cudaError_t e;
 #define TC_TRY(x) do { if ((e = (x)) != cudaSuccess) return e; } while (0)
-    TC_TRY(cudaFuncSetAttribute(k_tc_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-    TC_TRY(cudaFuncSetAttribute(k_tc_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    TC_TRY(cudaFuncSetAttribute(k_tc_scan<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    TC_TRY(cudaFuncSetAttribute(k_tc_scan<false, R_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    TC_TRY(cudaFuncSetAttribute(k_tc_scan<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     const size_t dsmem = (size_t)q.dpad * 4 + 4 * 32 * 33 * 4, ssmem = 4 * ((size_t)p.kp * 16 + 256);
     if (dsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     TC_TRY(cudaFuncSetAttribute(k_tc_exact_dist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
@@ -693,19 +800,25 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     a.sqn = c.sqn; a.deleted = c.deleted; a.first_slot = c.first_slot; a.n = c.n; a.nq = q.nq; a.nq_pad = p.nq_pad; a.kblocks = p.kblocks;
     a.metric = metric; a.n_tiles = p.n_tiles; a.tiles_per_slice = p.tiles_per_slice; a.sample_stride = p.stride;
     a.samp = S.samp; a.tau = S.tau; a.cand = S.cand; a.cnt = S.cnt; a.cap = p.cap;
+    if (const char* fe = getenv("VSANN_TC_FLAGS")) a.flags = (uint32_t)atoi(fe);
     const dim3 grid(p.nqt, p.slices);
-    k_tc_scan<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
-    const size_t thr_smem = (size_t)p.slices * (EPI_WARPS / 4) * R_MAX * 4;
+    {
+        ScanArgs as = a; as.tiles_per_slice = p.s_tiles_per_slice;
+        const dim3 sgrid(p.nqt, p.s_slices);
+        if (p.r <= 8) k_tc_scan<false, 8><<<sgrid, threads_of(false), SMEM_BYTES, st>>>(mapQ, mapX, as);
+        else k_tc_scan<false, R_MAX><<<sgrid, threads_of(false), SMEM_BYTES, st>>>(mapQ, mapX, as);
+    }
+    const size_t thr_smem = (size_t)p.s_slices * (EPI_WARPS / 4) * R_MAX * 4;
     if (thr_smem > 48 * 1024) TC_TRY(cudaFuncSetAttribute(k_tc_threshold, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)thr_smem));
     // sample rank whose key estimates the k-th neighbour's from above: ceil(k / stride) (rank 1 when the sample is sparser than k)
     const uint32_t r0 = std::max<uint32_t>(1u, std::min<uint32_t>(p.r > 1 ? p.r - 1 : 1u, (kplan + p.stride - 1) / p.stride));
     const char* we = getenv("VSANN_TC_WIDEN");   // 0 = sampled threshold as is (A/B switch)
-    k_tc_threshold<<<q.nq, THR_THREADS, thr_smem, st>>>(S.samp, p.slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, r0, S.tau, S.qn, S.ctr + 1, metric, q.dpad,
+    k_tc_threshold<<<q.nq, THR_THREADS, thr_smem, st>>>(S.samp, p.s_slices * (EPI_WARPS / 4), q.nq, p.nq_pad, p.r, r0, S.tau, S.qn, S.ctr + 1, metric, q.dpad,
                                                         p.stride, p.cap, (!we || atoi(we) != 0) ? 1 : 0);
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     const bool timing = stats && stats->time_scan && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess;
     if (timing) cudaEventRecord(ev0, st);
-    k_tc_scan<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapQ, mapX, a);
+    k_tc_scan<true, 1><<<grid, threads_of(true), SMEM_BYTES, st>>>(mapQ, mapX, a);
     if (timing) cudaEventRecord(ev1, st);
 
     RerankArgs r{};
@@ -738,7 +851,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
         ScanArgs a2 = a;
         a2.nq = cap2; a2.nq_pad = p2.nq_pad; a2.n_tiles = p2.n_tiles; a2.tiles_per_slice = p2.tiles_per_slice; a2.tau = S.r2_tau;
         a2.n_active = S.ctr; a2.active_cap = cap2;
-        k_tc_scan<true><<<dim3(p2.nqt, p2.slices), THREADS, SMEM_BYTES, st>>>(mapQ2, mapX, a2);
+        k_tc_scan<true, 1><<<dim3(p2.nqt, p2.slices), threads_of(true), SMEM_BYTES, st>>>(mapQ2, mapX, a2);
         RerankArgs r2 = r;
         r2.q = S.gq; r2.q_stride = q.dpad; r2.qn = S.r2_qn; r2.nq = cap2; r2.qmap = S.r2_ids; r2.tau = S.r2_tau; r2.n_r2 = nullptr; r2.n_active = S.ctr; r2.r2_cap = 0;
         k_tc_exact_dist<<<dim3(cap2, (p.cap + 127) / 128), 128, dsmem, st>>>(r2);
