@@ -816,6 +816,25 @@ def main():
                 t = timed(lambda: local_search(0, exact=True, nb=b), 3, 1, mark=False)
                 exact_by_batch[str(b)] = {"ms": t, "qps": b / t * 1e3, "tflops": 2.0 * b * n * d / t / 1e9, "corpus_gbs": n * d * 4.0 / t / 1e6}
 
+        # the tcgen05 TF32 rate of the same kernel on this GPU, measured instead of assumed: the scan without its epilogue arithmetic
+        # (TMA + MMA: what a plain GEMM loop of this tile shape reaches) and without its loads as well (the MMA issue rate alone);
+        # VSANN_TC_FLAGS is a measurement switch of exact_tc.cu - those two launches return right after the scan, their results are not used
+        tf32_measured = {}
+        if world == 1 and st_exact["exact_tc_scans"]:
+            for name, fl in (("tma_mma_no_epilogue", 8), ("mma_only", 24)):
+                os.environ["VSANN_TC_FLAGS"] = str(fl)
+                try:
+                    g.set_stats(True); g.reset_stats()
+                    for _ in range(3):
+                        local_search(0, exact=True)
+                    torch.cuda.synchronize()
+                    sv = g.stats()
+                    if sv["exact_tc_scans"] and sv["exact_tc_scan_seconds"] > 0:
+                        tf32_measured[name] = 2.0 * nq * n * d / (sv["exact_tc_scan_seconds"] / sv["exact_tc_scans"]) / 1e12
+                finally:
+                    os.environ.pop("VSANN_TC_FLAGS", None)
+                    g.set_stats(False)
+
     # ---- e2e: same batch through the C ABI with pinned HOST buffers (H2D + D2H inside) --------------
     qh = torch.from_numpy(q).pin_memory()
     kh = torch.empty((nq, k), dtype=torch.int64).pin_memory()
@@ -979,6 +998,7 @@ def main():
                      "roofline": {"bound": "tensor", "kernel": "k_tc_scan<EMIT>", "achieved": exact_tf, "peak": tf32_peak, "unit": "TFLOP/s",
                                   "frac": (exact_tf / tf32_peak) if exact_tf else None, "kernel_ms": scan_ms,
                                   "peak_source": "TF32 = half the measured bf16 burst rate (MEASURED_PEAKS.json bf16_tflops / 2)",
+                                  "tf32_tflops_measured_here": tf32_measured,
                                   "flops_per_launch": 2.0 * nq * n * d}}
         extra = {}
         if host_gen and S == 1 and not args.no_extra and args.dist == "clustered":

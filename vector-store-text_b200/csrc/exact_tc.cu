@@ -132,7 +132,8 @@ struct ScanArgs {
     float* samp;                                 // SAMPLE: [slices * EPI_WARPS / 4][nq_pad][R_MAX] ascending
     const float* tau; uint32_t* cand; uint32_t* cnt; uint32_t cap;   // EMIT
     const uint32_t* n_active; uint32_t active_cap;                    // second scan: the query count lives on the device (null = nq)
-    uint32_t flags;                                                   // A/B switches (VSANN_TC_FLAGS): 1 = queries not resident, 2 = coefficient loads one tile at a time, 4 = ids written at once
+    uint32_t flags;                                                   // A/B switches (VSANN_TC_FLAGS): 1 = queries not resident, 2 = coefficient loads one tile at a time, 4 = ids written at once,
+                                                                      // 8 = no epilogue arithmetic, 16 = no TMA loads (8 / 24: rate measurements, results are garbage)
 };
 
 // (a, b) of one corpus row: key = a * dot + b. In two halves, so that the coefficient warp can issue the loads of several tiles
@@ -205,11 +206,22 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
-            if (res_a && t_first < t_end) {
+            bool t_end_skip = false;
+            if (a.flags & 16u) {       // measurement: the MMAs run on whatever the shared memory holds
+                if (res_a && t_first < t_end) mbar_arrive(s32(&ctrl->afull));
+                for (uint32_t t = t_first; t < t_end; t += t_step)
+                    for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
+                        mbar_wait(s32(&ctrl->empty[stage]), phase ^ 1u);
+                        mbar_arrive(s32(&ctrl->full[stage]));
+                        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                t_end_skip = true;
+            }
+            if (res_a && t_first < t_end && !t_end_skip) {
                 mbar_expect_tx(s32(&ctrl->afull), a.kblocks * A_BYTES);
                 for (uint32_t kb = 0; kb < a.kblocks; ++kb) tma_load_2d(smem_s + kb * A_BYTES, &mapQ, s32(&ctrl->afull), (int)(kb * BK), (int)q0);
             }
-            for (uint32_t t = t_first; t < t_end; t += t_step) {
+            for (uint32_t t = t_first; t < t_end && !t_end_skip; t += t_step) {
                 for (uint32_t kb = 0; kb < a.kblocks; ++kb) {
                     mbar_wait(s32(&ctrl->empty[stage]), phase ^ 1u);
                     const uint32_t full = s32(&ctrl->full[stage]);
@@ -360,9 +372,9 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
             };
 #ifndef TC_DEBUG_SKIP_EPI
             float va[32], vb[32];
-            tmem_ld32_issue(taddr, va);
+            if (!(a.flags & 8u)) tmem_ld32_issue(taddr, va);
 #pragma unroll 1
-            for (int c = 0; c < EPI_COLS / 32; c += 2) {
+            for (int c = 0; c < EPI_COLS / 32 && !(a.flags & 8u); c += 2) {
                 tmem_wait();
                 tmem_ld32_issue(taddr + (c + 1) * 32, vb);
                 process(va, c);
@@ -820,6 +832,14 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     if (timing) cudaEventRecord(ev0, st);
     k_tc_scan<true, 1><<<grid, threads_of(true), SMEM_BYTES, st>>>(mapQ, mapX, a);
     if (timing) cudaEventRecord(ev1, st);
+    if (a.flags & 24u) {   // rate measurement (bench.py: tcgen05 TF32 rate of this kernel without its epilogue / without its loads): nothing to re-rank
+        TC_TRY(cudaStreamSynchronize(st));
+        if (timing) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) stats->scan_ms += ms; }
+        if (stats) stats->scans++;
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        return cudaSuccess;
+    }
 
     RerankArgs r{};
     r.vecs = c.vecs; r.sqn = c.sqn; r.slot_key = c.slot_key; r.deleted = c.deleted; r.first_slot = c.first_slot; r.n_slots = c.n_slots; r.dpad = q.dpad;
