@@ -526,6 +526,14 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if os.environ.get("VSANN_BENCH_PIN") == "1" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # experiment: every rank on its own slice of the host cores (torchrun does not pin; a migrating launch thread shows up in every
+        # rank's step, because every step ends in a barrier)
+        try:
+            cores = sorted(os.sched_getaffinity(0)); w = int(os.environ["WORLD_SIZE"]); per = max(1, len(cores) // w)
+            os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
+        except Exception:   # noqa: BLE001
+            pass
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -680,6 +688,7 @@ def main():
         except Exception as e:   # noqa: BLE001
             print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]}); using NCCL all_gather", file=sys.stderr)
             p2p = None
+    align_starts = os.environ.get("VSANN_BENCH_ALIGN", "1") != "0"
     exchange = (p2p.describe() if p2p else "nccl all_gather + merge kernel") if world > 1 else (
         f"one vs_index over {G} devices in one process: fan-out on {G} streams, merge kernel on device 0 over peer mappings" if G > 1 else "none")
 
@@ -693,8 +702,7 @@ def main():
         if world == 1:
             return local_search(ef, exact)
         if p2p:
-            i, kp, dp = p2p.next_buffer()
-            g.search_device(nq, qd.data_ptr(), k, kp, dp, ef=ef, exact=exact, stream=stream)
+            i = p2p.search(g, nq, qd.data_ptr(), ef=ef, exact=exact, stream=stream)
             p2p.merge(i, mk, md)
             return mk
         local_search(ef, exact)
@@ -757,6 +765,11 @@ def main():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             if world > 1:
                 dist.barrier()
+                if p2p is not None and align_starts:
+                    # the ranks leave the NCCL barrier (a host wait) tens of microseconds apart, and a rank that starts early would count
+                    # the others' lateness as exchange time; in service the ranks ARE aligned (every step ends in the merge's flag
+                    # barrier). One device-side barrier kernel on the timed stream, BEFORE the first event, puts them back in step.
+                    p2p.fhdl.barrier(channel=1)
             e0.record(ts)
             fn()
             e1.record(ts)
@@ -842,13 +855,14 @@ def main():
     fh = np.zeros(nq, dtype=np.uintp)
     fn_host = getattr(lib, "vs_search_batch")
 
-    def e2e_step():
+    def e2e_step(mode):
         if world > 1 and p2p:
-            # sharded serving path: the traversal kernel reads the pinned HOST queries in place (vs_search_batch_device accepts any
-            # device-accessible pointer; page-locked memory is one under UVA) and writes the shard's lists into symmetric memory,
-            # the fused gather + merge follows on the same stream, only the merged top-k goes back to the host
-            i, kp, dp = p2p.next_buffer()
-            g.search_device(nq, qh.data_ptr(), k, kp, dp, ef=chosen, stream=stream)
+            # sharded serving path: the traversal kernel reads the pinned HOST queries where they lie (vs_search_batch*_device accept any
+            # device-accessible pointer; page-locked memory is one under UVA), the shard's lists go to symmetric memory (pushed to every
+            # peer while the traversal runs), the fused barrier + merge follows on the same stream, and only the merged top-k goes back
+            # to the host. (Measured and dropped: every rank uploading 1 / N of the block and gathering the rest over NVLink - three more
+            # launches per step cost more than the host traffic they save: 0.70 against 0.62 ms at N = 2, equal at N = 8.)
+            i = p2p.search(g, nq, qh.data_ptr(), ef=chosen, stream=stream)
             p2p.merge(i, mk, md)
             kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
             ts.synchronize()
@@ -862,19 +876,60 @@ def main():
             kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
             ts.synchronize()
 
-    for _ in range(max(1, args.warmup)):
-        e2e_step()
-    barrier()
     import gc
-    gc.collect(); gc.disable()          # a collection inside a 6 ms region would be a tenth of it
-    sampler.mark(True)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
-    sampler.mark(False)
-    gc.enable()
+    e2e_modes = ["in_place"] if (world > 1 and p2p) else ["c_abi_host_buffers"]
+    e2e_by_mode = {}
+    for mode in e2e_modes:
+        for _ in range(max(1, args.warmup)):
+            e2e_step(mode)
+        barrier()
+        gc.collect(); gc.disable()          # a collection inside a 6 ms region would be a tenth of it
+        if mode == e2e_modes[0]:
+            sampler.mark(True)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step(mode)
+        torch.cuda.synchronize()
+        e2e_by_mode[mode] = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+        if mode == e2e_modes[0]:
+            sampler.mark(False)
+        gc.enable()
+        e2e_recall_m = recall(kh.numpy().view(np.uint64), truth)
+        if mode == e2e_modes[0]:
+            e2e_recall = e2e_recall_m
+    e2e_mode = e2e_modes[0]                 # the headline is the path the package takes by default, whatever the other one measured
+    # where an end-to-end step goes (not timed into anything): host time until everything is enqueued, device time from the first
+    # launch to the merged result and to the end of the copies, wall time of the whole step - per rank, max and mean over ranks
+    e2e_breakdown = None
+    if os.environ.get("VSANN_BENCH_E2E_TRACE", "1" if world > 1 else "0") != "0" and world > 1 and p2p:
+        e2e_breakdown = {}
+        names = ("host_enqueue", "device_first_launch_to_merged", "device_to_end_of_copies", "wall_step")
+        for mode in e2e_modes:
+            acc = np.zeros(4)
+            n_tr = max(10, args.steps)
+            barrier()
+            for it in range(n_tr + 3):
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                t0 = time.perf_counter()
+                ev[0].record(ts)
+                i = p2p.search(g, nq, qh.data_ptr(), ef=chosen, stream=stream)
+                p2p.merge(i, mk, md)
+                ev[1].record(ts)
+                kh.copy_(mk, non_blocking=True); dh.copy_(md, non_blocking=True)
+                ev[2].record(ts)
+                t1 = time.perf_counter()
+                ts.synchronize()
+                t2 = time.perf_counter()
+                if it >= 3:
+                    acc += np.array([(t1 - t0) * 1e3, ev[0].elapsed_time(ev[1]), ev[0].elapsed_time(ev[2]), (t2 - t0) * 1e3])
+            acc /= n_tr
+            tmax = torch.tensor(acc, device=dev); tsum = tmax.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX); dist.all_reduce(tsum)
+            e2e_breakdown[mode] = {"ms_max_over_ranks": dict(zip(names, [round(float(x), 4) for x in tmax.cpu()])),
+                                   "ms_mean_over_ranks": dict(zip(names, [round(float(x) / world, 4) for x in tsum.cpu()]))}
+        if rank == 0:
+            log(f"e2e breakdown: {e2e_breakdown}")
+    e2e_ms = e2e_by_mode[e2e_mode]
     if world == 1 and rank == 0 and sampler.need_tail():
         # the sampler was too slow for the millisecond-scale regions above (nvidia-smi fallback): keep the timed
         # step itself running (not timed again) until it has seen the clocks under the same load
@@ -885,7 +940,6 @@ def main():
             torch.cuda.synchronize()
         sampler.mark(False)
     clocks = sampler.stop() if rank == 0 else None
-    e2e_recall = recall(kh.numpy().view(np.uint64), truth)
 
     # kernel-side work counters at the operating point (every rank: the device counters cost atomics, so outside the timed regions)
     g.set_stats(True); g.reset_stats()
@@ -1016,7 +1070,9 @@ def main():
                                 "ef_sweep_recall_shard_alone": sweep_local, "ef_sweep_recall": sweep,
                                 "smallest_ef_global": {"ef_search": ef_global, "recall_at_k": sweep.get(ef_global), "ms_per_step": ms_global_ef,
                                                        "qps": nq / (ms_global_ef * 1e-3)},
-                                "exchange": exchange},
+                                "exchange": exchange,
+                                "timed_step_start": ("ranks aligned by a device-side barrier kernel before the first event (VSANN_BENCH_ALIGN=0: NCCL barrier only)"
+                                                     if (world > 1 and p2p is not None and align_starts) else "barrier + synchronize")},
             "value_definition": ("queries answered per second against the whole corpus of corpus_total vectors "
                                  "(weak scaling: the corpus grows N x at fixed per-GPU work, so the ideal curve is FLAT; see shard_queries_per_s)"
                                  if cfg["scaling"] == "weak" else "queries answered per second against the whole corpus (split over the ranks)"),
@@ -1024,8 +1080,8 @@ def main():
             "parity_point": {"ef_search": parity_ef, "recall_at_k": sweep.get(parity_ef), "qps": nq / (ms_parity * 1e-3)},
             "parity_at_bench": parity_at_bench,
             "build": build,
-            "e2e": {"value": nq / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12,
-                    "ms_per_step": e2e_ms, "recall_at_k": e2e_recall},
+            "e2e": {"value": nq / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4 * world, "d2h_bytes_per_step": nq * k * 12 * world,
+                    "ms_per_step": e2e_ms, "recall_at_k": e2e_recall, "path": e2e_mode, "ms_per_step_by_path": e2e_by_mode, "breakdown": e2e_breakdown},
             "gpu_launches": args.steps * (1 if S == 1 else (G + 1 if G > 1 else 2)),   # per step: k_search_t per shard (+ the merge kernel after the exchange)
             "by_batch": by_batch or None, "recall_sweep": recall_sweep,
             "exact": exact,

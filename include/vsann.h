@@ -146,6 +146,14 @@ vs_status vs_search_batch(vs_index* index, size_t nq, const float* queries, size
 vs_status vs_search_batch_device(vs_index* index, size_t nq, const float* d_queries, size_t k,
                                  size_t ef_override, int exact,
                                  uint64_t* d_keys_out, float* d_dist_out, void* stream);
+/* The same graph search with every query's result list written to n_out (1..9) buffers: d_keys_out[0] / d_dist_out[0] is
+ * the index's device, the others may be ANY device-writable memory - other GPUs' buffers mapped over NVLink / NVSwitch in a
+ * sharded deployment (one index per GPU): a shard's lists reach every peer while its traversal is still
+ * running, and the exchange step that follows (vs_merge_topk_flags_device) reads local memory only. Graph search on a
+ * single-device index only (exact mode and multi-device indexes: VS_ERR_UNSUPPORTED). No counterpart in the reference, whose
+ * index lives in one process (usearch.rs:98). */
+vs_status vs_search_batch_fanout_device(vs_index* index, size_t nq, const float* d_queries, size_t k, size_t ef_override,
+                                        size_t n_out, uint64_t* const* d_keys_out, float* const* d_dist_out, void* stream);
 
 /* usearch::Index::size / capacity / reserve — usearch.rs:201-206,309. */
 size_t vs_count(vs_index* index);

@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol(vst):
 
 def test_oracle_exports_same_abi(oracle_lib):
     for s in header_symbols():
-        if s in ("vs_add_batch_device", "vs_search_batch_device", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_merge_topk_flags_device", "vs_exact_search_noalloc_device", "vs_export_level"):
+        if s in ("vs_add_batch_device", "vs_search_batch_device", "vs_search_batch_fanout_device", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_merge_topk_flags_device", "vs_exact_search_noalloc_device", "vs_export_level"):
             continue   # device-pointer entry points have no CPU meaning
         if s in ("vs_index_save", "vs_index_load"):
             continue   # persistence is not part of the reference's algorithm (it has none): nothing to restate

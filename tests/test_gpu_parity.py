@@ -241,6 +241,8 @@ def test_merge_topk_peers_device(vst, parts, nq, k):
     if k > 4:
         dist[1, :, 3] = dist[0, :, 4]                                     # cross-part ties -> key order
         dist = np.sort(dist, axis=2)
+        dist[0, ::2, k - 2:] = np.inf; keys[0, ::2, k - 2:] = np.iinfo(np.uint64).max      # short lists: padded tails, equal across parts
+        dist[parts - 1, ::3, k - 1:] = np.inf; keys[parts - 1, ::3, k - 1:] = np.iinfo(np.uint64).max
     pk = [torch.from_numpy(keys[p].view(np.int64).copy()).cuda() for p in range(parts)]
     pd = [torch.from_numpy(dist[p].copy()).cuda() for p in range(parts)]
     kp = torch.tensor([t.data_ptr() for t in pk], dtype=torch.int64, device="cuda")
@@ -253,6 +255,35 @@ def test_merge_topk_peers_device(vst, parts, nq, k):
         allp = sorted(zip(dist[:, i, :].ravel().tolist(), keys[:, i, :].ravel().tolist()))[:k]
         assert odh[i].tolist() == [p[0] for p in allp]
         assert okh[i].tolist() == [p[1] for p in allp]
+
+
+def test_search_fanout_writes_every_buffer(vst):
+    """vs_search_batch_fanout_device: the lists of a graph search land in all n_out buffers (peer GPUs' memory in the sharded
+    deployment, separate local allocations here), equal to what vs_search_batch_device writes - for the warp-per-query kernel
+    (2000 queries) and the block-per-query kernel (40 queries); exact mode and too many buffers are refused."""
+    import ctypes as C
+    import torch
+    n, d, k = 20000, 64, 10
+    x = make_data(n, d, 81, clustered=True)
+    g = vst.VsIndex(d, metric=1, capacity_hint=n)
+    g.add_batch(np.arange(n, dtype=np.uint64) * 3 + 1, x)
+    for nq in (2000, 40):
+        q = torch.from_numpy(make_data(nq, d, 82 + nq, clustered=True)).cuda()
+        ok = torch.empty((nq, k), dtype=torch.int64, device="cuda"); od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        g.search_device(nq, q.data_ptr(), k, ok.data_ptr(), od.data_ptr(), ef=32)
+        torch.cuda.synchronize()
+        for n_out in (1, 4, 9):
+            ks = [torch.full((nq, k), -5, dtype=torch.int64, device="cuda") for _ in range(n_out)]
+            ds = [torch.full((nq, k), -5.0, dtype=torch.float32, device="cuda") for _ in range(n_out)]
+            g.search_fanout_device(nq, q.data_ptr(), k, [t.data_ptr() for t in ks], [t.data_ptr() for t in ds], ef=32)
+            torch.cuda.synchronize()
+            for t, u in zip(ks, ds):
+                assert torch.equal(t, ok) and torch.equal(u.view(torch.int32), od.view(torch.int32))
+    lib = vst.load_library()
+    ka = (C.c_void_p * 10)(*[ok.data_ptr()] * 10); da = (C.c_void_p * 10)(*[od.data_ptr()] * 10)
+    assert lib.vs_search_batch_fanout_device(g._h, 4, C.c_void_p(q.data_ptr()), k, 0, 10, ka, da, None) == vst.VS_ERR_UNSUPPORTED
+    assert lib.vs_search_batch_fanout_device(g._h, 4, C.c_void_p(q.data_ptr()), k, 0, 0, ka, da, None) == vst.VS_ERR_UNSUPPORTED
+    g.close()
 
 
 def test_device_resident_search_and_add(vst):

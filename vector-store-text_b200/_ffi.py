@@ -10,7 +10,7 @@ VS_OK, VS_ERR_INVALID, VS_ERR_DIMS, VS_NOT_FOUND, VS_ERR_CAPACITY, VS_ERR_CUDA, 
 
 ABI_SYMBOLS = [
     "vs_index_create", "vs_index_destroy", "vs_add", "vs_add_batch", "vs_add_batch_device", "vs_remove",
-    "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_count", "vs_capacity", "vs_reserve",
+    "vs_search", "vs_search_batch", "vs_search_batch_device", "vs_search_batch_fanout_device", "vs_count", "vs_capacity", "vs_reserve",
     "vs_flush", "vs_get_stats", "vs_set_stats", "vs_reset_stats", "vs_merge_topk_device", "vs_merge_topk_peers_device", "vs_export_level",
     "vs_merge_topk_flags_device", "vs_exact_search_noalloc_device", "vs_index_save", "vs_index_load", "vs_last_error", "vs_version",
 ]
@@ -95,6 +95,7 @@ def load_library(path: str = None, prefix: str = "vs_"):
         sig.update({
             "add_batch_device": (C.c_int, [vp, C.c_size_t, u64p, vp]),
             "search_batch_device": (C.c_int, [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_int, vp, vp, vp]),
+            "search_batch_fanout_device": (C.c_int, [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp]),
             "merge_topk_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "merge_topk_peers_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp, vp]),
             "merge_topk_flags_device": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp]),
@@ -253,6 +254,14 @@ class VsIndex:
         self._check(self._fn("search_batch_device")(self._h, int(nq), C.c_void_p(int(q_ptr)), int(k), int(ef), 1 if exact else 0,
                                                     C.c_void_p(int(keys_ptr)), C.c_void_p(int(dist_ptr)),
                                                     C.c_void_p(int(stream)) if stream else None))
+
+    def search_fanout_device(self, nq, q_ptr, k, keys_ptrs, dist_ptrs, ef=0, stream=0):
+        """Graph search whose result lists go to every (keys, dists) buffer pair: keys_ptrs / dist_ptrs are sequences of device-
+        writable addresses (the first pair on the index's device, the others e.g. peer GPUs' memory)."""
+        n = len(keys_ptrs)
+        ka = (C.c_void_p * n)(*[int(p) for p in keys_ptrs]); da = (C.c_void_p * n)(*[int(p) for p in dist_ptrs])
+        self._check(self._fn("search_batch_fanout_device")(self._h, int(nq), C.c_void_p(int(q_ptr)), int(k), int(ef), n, ka, da,
+                                                           C.c_void_p(int(stream)) if stream else None))
 
     def count(self):
         return int(self._fn("count")(self._h))

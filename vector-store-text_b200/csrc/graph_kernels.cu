@@ -112,13 +112,24 @@ __global__ void __launch_bounds__(128, 8) k_search_r(GraphView g, const float* _
     }
 }
 
+// Copies of a query's finished result list into up to 8 more buffers - other GPUs' memory mapped over NVLink / NVSwitch in the sharded
+// search (vs_search_batch_fanout_device): the lists travel while the traversal of the other queries is still running, and the merge
+// that follows reads local memory only. The warp re-reads what it has just written (ordered by the __syncwarp before the call).
+__device__ __forceinline__ void fan_out(const OutFan& fan, uint32_t q, uint32_t k, const uint64_t* ko, const float* dd) {
+    if (fan.n == 0) return;
+    for (uint32_t i = lane_id(); i < k; i += 32) {
+        const uint64_t key = ko[i]; const float d = dd[i];
+        for (uint32_t r = 0; r < fan.n; ++r) { fan.keys[r][(size_t)q * k + i] = key; fan.dist[r][(size_t)q * k + i] = d; }
+    }
+}
+
 // Bulk-copy staged variant (tbeam.cuh): the default K3. NL = list rows (ef <= 32 NL), CPL = query
 // float4 chunks a lane keeps in registers (chunks == 8 CPL), 0 = any dims (query read from shared memory).
 template <int NL, int CPL>
 __global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : (NL <= 16 ? 4 : 3))) k_search_t(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries, uint32_t nq, uint32_t k,
                                                      uint32_t ef, uint32_t hsize, uint32_t stage_rows,
                                                      uint64_t* __restrict__ keys_out, float* __restrict__ dist_out,
-                                                     unsigned long long* counters, uint32_t* work) {
+                                                     unsigned long long* counters, uint32_t* work, const OutFan fan) {
     extern __shared__ __align__(128) unsigned char smem[];
     const unsigned warp = threadIdx.x >> 5, lane = lane_id();
     const size_t per_warp = tsmem_bytes(g.dpad, hsize, stage_rows);
@@ -148,6 +159,7 @@ __global__ void __launch_bounds__(128, (NL <= 8 ? VSANN_T_MINB : (NL <= 16 ? 4 :
         for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
         ++done;
         __syncwarp();
+        fan_out(fan, q, k, ko, dd);
     }
     if (counters && lane == 0) {
         atomicAdd(&counters[0], (unsigned long long)done);
@@ -195,7 +207,7 @@ __device__ __forceinline__ float blk_dist32(const GraphView& g, WarpSmem& S, War
 template <int NL, int CPL>
 __global__ void __launch_bounds__(256) k_search_blk(const __grid_constant__ CUtensorMap vmap, int use_vmap, GraphView g, const float* __restrict__ queries,
                                                     uint32_t nq, uint32_t k, uint32_t ef, uint32_t hsize, uint32_t stage_rows,
-                                                    uint64_t* __restrict__ keys_out, float* __restrict__ dist_out, unsigned long long* counters) {
+                                                    uint64_t* __restrict__ keys_out, float* __restrict__ dist_out, unsigned long long* counters, const OutFan fan) {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ BlkShared B;
     const unsigned warp = threadIdx.x >> 5, lane = lane_id();
@@ -282,6 +294,8 @@ __global__ void __launch_bounds__(256) k_search_blk(const __grid_constant__ CUte
     }
     if (warp == 0) {
         for (uint32_t i = nout + lane; i < k; i += 32) { ko[i] = 0xFFFFFFFFFFFFFFFFull; dd[i] = INFINITY; }
+        __syncwarp();
+        fan_out(fan, q, k, ko, dd);
         if (counters && lane == 0) {
             atomicAdd(&counters[0], 1ull);
             atomicAdd(&counters[1], (unsigned long long)evals);
@@ -692,30 +706,36 @@ __global__ void k_merge_topk(uint32_t parts, uint32_t nq, uint32_t k, const uint
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
 
+// The barrier half of the fused exchange (see below): called by every thread of every block.
+__device__ __forceinline__ void merge_gate(uint32_t* const* __restrict__ flags, uint32_t parts, uint32_t my_part, uint32_t epoch) {
+    if (blockIdx.x == 0) {
+        // ONE block per GPU polls the peers: thousands of pollers on a peer's flag word contend with that peer's traversal
+        // kernel for its NVLink ingress (measured at N = 2: end-to-end step 0.80 ms with every block polling, against 0.64 ms).
+        // One LANE per peer: a poll is an NVLink round trip, seven of them in a row were most of the barrier at N = 8.
+        if (threadIdx.x < 32) {
+            uint32_t* mine = flags[my_part];      // word 0: what the peers read; word 1: "every peer has arrived", read by this GPU's other blocks
+            if (threadIdx.x == 0) { __threadfence_system(); st_release_sys(mine, epoch); }
+            for (uint32_t p = threadIdx.x; p < parts; p += 32) {
+                if (p == my_part) continue;
+                while ((int32_t)(ld_acquire_sys(flags[p]) - epoch) < 0) __nanosleep(200);
+            }
+            __syncwarp();
+            if (threadIdx.x == 0) { __threadfence(); asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine + 1), "r"(epoch) : "memory"); }
+        }
+    } else if (threadIdx.x == 0) {
+        const uint32_t* mine = flags[my_part];
+        uint32_t v;
+        do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + 1) : "memory"); if ((int32_t)(v - epoch) < 0) __nanosleep(100); } while ((int32_t)(v - epoch) < 0);
+    }
+    __syncthreads();
+}
+
 template <bool STAGED>
 __global__ void k_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const uint64_t* const* __restrict__ part_keys,
                                   const float* const* __restrict__ part_dist, uint32_t* const* __restrict__ flags, uint32_t my_part, uint32_t epoch,
                                   uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
     extern __shared__ __align__(16) unsigned char msm[];
-    if (flags) {
-        if (threadIdx.x == 0) {
-            uint32_t* mine = flags[my_part];      // word 0: what the peers read; word 1: "every peer has arrived", read by this GPU's other blocks
-            if (blockIdx.x == 0) {
-                // ONE thread per GPU polls the peers: thousands of pollers on a peer's flag word contend with that peer's traversal
-                // kernel for its NVLink ingress (measured at N = 2: end-to-end step 0.80 ms with every block polling, against 0.64 ms)
-                __threadfence_system(); st_release_sys(mine, epoch);
-                for (uint32_t p = 0; p < parts; ++p) {
-                    if (p == my_part) continue;
-                    while ((int32_t)(ld_acquire_sys(flags[p]) - epoch) < 0) __nanosleep(200);
-                }
-                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine + 1), "r"(epoch) : "memory");
-            } else {
-                uint32_t v;
-                do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + 1) : "memory"); if ((int32_t)(v - epoch) < 0) __nanosleep(100); } while ((int32_t)(v - epoch) < 0);
-            }
-        }
-        __syncthreads();
-    }
+    if (flags) merge_gate(flags, parts, my_part, epoch);
     const uint32_t warp = threadIdx.x >> 5, q = blockIdx.x * (blockDim.x >> 5) + warp, lane = lane_id();
     if (q >= nq) return;
     const uint32_t tot = parts * k;
@@ -749,6 +769,69 @@ __global__ void k_merge_topk_ptrs(uint32_t parts, uint32_t nq, uint32_t k, const
         }
         if (lane == 0) { keys_out[(size_t)q * k + o] = wk; dist_out[(size_t)q * k + o] = wd; }
         if (wp != NONE && (wp & 31u) == lane) ++head[wp >> 5];
+    }
+}
+
+// The same exchange for lists that fit shared memory, QB queries per block: measured on two B200s with every list ready, the
+// warp-per-query tournament above took 46 us for 10 000 x 10 lists from 2 parts and 123 us for 4096 x 100 (the flag barrier only
+// 8 us of the fused kernel): k dependent rounds of a 32-lane reduction to find ONE output, and a few 8-byte peer loads per lane.
+// Here the block pulls the lists of its QB queries from every part with coalesced loads (a part's lists of consecutive queries are
+// one contiguous run), and every (query, part, position) element finds its OWN place in the merged order: position + the number
+// of elements of the other parts that precede it - a binary search per other part over its sorted list, no rounds, no shuffles.
+// Order: (distance, key), then part for full ties (padding entries) - the order of k_merge_topk / merge_topk_host.
+__global__ void __launch_bounds__(256) k_merge_topk_rank(uint32_t parts, uint32_t nq, uint32_t k, uint32_t qb, const uint64_t* const* __restrict__ part_keys,
+                                                         const float* const* __restrict__ part_dist, uint32_t* const* __restrict__ flags, uint32_t my_part,
+                                                         uint32_t epoch, uint64_t* __restrict__ keys_out, float* __restrict__ dist_out) {
+    extern __shared__ __align__(16) unsigned char msm[];
+    if (flags) merge_gate(flags, parts, my_part, epoch);
+    const uint32_t q0 = blockIdx.x * qb;
+    if (q0 >= nq) return;
+    const uint32_t nqb = min(qb, nq - q0), per_part = nqb * k;
+    uint64_t* sk = reinterpret_cast<uint64_t*>(msm);                              // [part][query][k]
+    float* sd = reinterpret_cast<float*>(msm + (size_t)parts * qb * k * 8);
+    // all parts' loads of an element leave before any of them is stored: one NVLink round trip per block, not one per peer
+    for (uint32_t p0 = 0; p0 < parts; p0 += 8) {
+        const uint64_t* gk[8]; const float* gd[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { const uint32_t p = min(p0 + u, parts - 1); gk[u] = part_keys[p] + (size_t)q0 * k; gd[u] = part_dist[p] + (size_t)q0 * k; }
+        for (uint32_t i = threadIdx.x; i < per_part; i += blockDim.x) {
+            uint64_t kk[8]; float dd[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (p0 + u < parts) { kk[u] = gk[u][i]; dd[u] = gd[u][i]; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (p0 + u < parts) { sk[(size_t)(p0 + u) * qb * k + i] = kk[u]; sd[(size_t)(p0 + u) * qb * k + i] = dd[u]; }
+        }
+    }
+    __syncthreads();
+    // bound[q] = the smallest LAST distance over the parts: that part alone holds k entries <= bound, so nothing beyond it can be
+    // among the k best (with 8 parts seven eighths of the entries leave here, before any search)
+    float* bound = reinterpret_cast<float*>(msm + (size_t)parts * qb * k * 12);
+    for (uint32_t ql = threadIdx.x; ql < nqb; ql += blockDim.x) {
+        float b = INFINITY;
+        for (uint32_t p = 0; p < parts; ++p) b = fminf(b, sd[(size_t)p * qb * k + ql * k + (k - 1)]);
+        bound[ql] = b;
+    }
+    __syncthreads();
+    const uint32_t total = parts * per_part;
+    for (uint32_t e = threadIdx.x; e < total; e += blockDim.x) {
+        const uint32_t p = e / per_part, r = e - p * per_part, ql = r / k, j = r - ql * k;
+        const float d = sd[(size_t)p * qb * k + r]; const uint64_t key = sk[(size_t)p * qb * k + r];
+        if (d > bound[ql]) continue;
+        uint32_t rank = j;
+        for (uint32_t o = 0; o < parts && rank < k; ++o) {
+            if (o == p) continue;
+            const float* od = sd + (size_t)o * qb * k + ql * k; const uint64_t* ok = sk + (size_t)o * qb * k + ql * k;
+            // number of entries of part o that precede (d, key, p): lower bound for o > p, upper bound for o < p
+            uint32_t lo = 0, hi = min(k, k - rank);      // more than k - rank of them would put this element past the output anyway
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                const float md = od[mid]; const uint64_t mk = ok[mid];
+                const bool before = md < d || (md == d && (mk < key || (mk == key && o < p)));
+                if (before) lo = mid + 1; else hi = mid;
+            }
+            rank += lo;
+        }
+        if (rank < k) { keys_out[(size_t)(q0 + ql) * k + rank] = key; dist_out[(size_t)(q0 + ql) * k + rank] = d; }
     }
 }
 
@@ -810,7 +893,7 @@ static inline uint32_t hash_size_for(uint32_t ef, const DeviceInfo& dev, const G
 
 template <int NL, int CPL>
 static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                                   uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+                                   uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan& fan) {
     const uint32_t rows = stage_rows_for(g, dev), hs = hash_size_for(ef, dev, g, rows);
     uint32_t wpb = 4;
     // wide lists (ef > 256: NL = 16 / 32 list registers per lane) with long rows: fewer warps per block so that hash + staging fit
@@ -823,15 +906,15 @@ static cudaError_t launch_search_t(const GraphView& g, const float* d_queries, u
     if ((e = next_work_counter(dev, st, &work)) != cudaSuccess) return e;
     const uint32_t blocks = std::min<uint32_t>((nq + wpb - 1) / wpb, (uint32_t)dev.sm_count * (NL <= 8 ? VSANN_T_MINB : 8));
     CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
-    k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work);
+    k_search_t<NL, CPL><<<blocks, wpb * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, work, fan);
     return cudaGetLastError();
 }
 template <int NL>
 static cudaError_t launch_search_tc(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
-    if (g.chunks == 32) return launch_search_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-    if (g.chunks == 24) return launch_search_t<NL, 3>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-    return launch_search_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+                                    uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan& fan) {
+    if (g.chunks == 32) return launch_search_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+    if (g.chunks == 24) return launch_search_t<NL, 3>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+    return launch_search_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
 }
 
 template <int NL, int CPL>
@@ -874,7 +957,7 @@ static cudaError_t launch_search_r(const GraphView& g, const float* d_queries, u
 
 template <int NL, int CPL>
 static cudaError_t launch_search_blk_t(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan& fan) {
     const uint32_t rows = stage_rows_for(g, dev), hs = hash_size_for(ef, dev, g, rows);
     const size_t per_warp = tsmem_bytes(g.dpad, hs, rows);
     uint32_t W = 8;
@@ -884,42 +967,44 @@ static cudaError_t launch_search_blk_t(const GraphView& g, const float* d_querie
     cudaError_t e = cudaFuncSetAttribute(k_search_blk<NL, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     CUtensorMap vmap; const int use_vmap = vecs_tmap(g, dev, &vmap);
-    k_search_blk<NL, CPL><<<nq, W * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters);
+    k_search_blk<NL, CPL><<<nq, W * 32, smem, st>>>(vmap, use_vmap, g, d_queries, nq, k, ef, hs, rows, d_keys, d_dist, counters, fan);
     return cudaGetLastError();
 }
 template <int NL>
 static cudaError_t launch_search_blk_c(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
-    if (g.chunks == 32) return launch_search_blk_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-    return launch_search_blk_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+                                       uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan& fan) {
+    if (g.chunks == 32) return launch_search_blk_t<NL, 4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+    return launch_search_blk_t<NL, 0>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
 }
 
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st) {
+                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan* fan_in) {
+    const OutFan fan = fan_in ? *fan_in : OutFan{};
     if (nq == 0) return cudaSuccess;
     // small batches: a block per query (K3b) - the SMs would idle otherwise and each query is latency bound on one warp
     static const uint32_t blk_max = [] { const char* e = getenv("VSANN_BLOCK_QUERY_MAX"); return e ? (uint32_t)atoi(e) : 0xFFFFFFFFu; }();
     const uint32_t blk_limit = blk_max != 0xFFFFFFFFu ? blk_max : 2u * (uint32_t)dev.sm_count;
     if (dev.stage_bytes && !dev.force_smem_list && ef <= 256 && nq <= blk_limit) {
         cudaError_t e;
-        if (ef <= 32) e = launch_search_blk_c<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else if (ef <= 64) e = launch_search_blk_c<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else if (ef <= 128) e = launch_search_blk_c<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else e = launch_search_blk_c<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (ef <= 32) e = launch_search_blk_c<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else if (ef <= 64) e = launch_search_blk_c<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else if (ef <= 128) e = launch_search_blk_c<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else e = launch_search_blk_c<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
         if (e != cudaErrorInvalidConfiguration) return e;
     }
     if (dev.stage_bytes && !dev.force_smem_list && ef <= 1024) {
         cudaError_t e;
-        if (ef <= 32) e = launch_search_tc<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else if (ef <= 64) e = launch_search_tc<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else if (ef <= 128) e = launch_search_tc<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else if (ef <= 256) e = launch_search_tc<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        if (ef <= 32) e = launch_search_tc<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else if (ef <= 64) e = launch_search_tc<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else if (ef <= 128) e = launch_search_tc<4>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else if (ef <= 256) e = launch_search_tc<8>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
         // ef up to 1024 (configs[4]'s recall sweep): the register list still beats the shared-memory list kernel
         // (5M x 1536, k = 100: ef = 512 took 67 ms per 4096 queries there against 17.6 ms at ef = 256)
-        else if (ef <= 512) e = launch_search_tc<16>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
-        else e = launch_search_tc<32>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
+        else if (ef <= 512) e = launch_search_tc<16>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
+        else e = launch_search_tc<32>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st, fan);
         if (e != cudaErrorInvalidConfiguration) return e;   // rows too long for the staging area: register-gather kernels below
     }
+    if (fan.n) return cudaErrorNotSupported;       // the register-gather and shared-memory-list kernels write one result buffer only
     if (!dev.force_smem_list) {
         if (ef <= 32) return launch_search_r<1>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
         if (ef <= 64) return launch_search_r<2>(g, d_queries, nq, k, ef, dev, d_keys, d_dist, counters, st);
@@ -1050,6 +1135,20 @@ cudaError_t launch_merge_topk_flags(uint32_t parts, uint32_t nq, uint32_t k, con
     if (k == 0 || parts == 0) return cudaSuccess;
     if (nq == 0 && !flags) return cudaSuccess;
     if (parts > 128) return cudaErrorInvalidValue;
+    // lists that fit shared memory: QB queries per block through the rank merge
+    const size_t per_query = (size_t)parts * k * 12;
+    const char* me = getenv("VSANN_MERGE_RANK");       // 0 = the warp tournament (A/B switch)
+    if (per_query <= 64 * 1024 && !(me && atoi(me) == 0)) {
+        uint32_t qb = (uint32_t)std::min<size_t>(32, (64 * 1024) / per_query);
+        while (qb > 1 && (nq + qb - 1) / qb < 2u * 148u) qb = (qb + 1) / 2;          // small batches: enough blocks to fill the GPU
+        const size_t smem = (size_t)qb * per_query + (size_t)qb * 4;
+        cudaError_t e = cudaFuncSetAttribute(k_merge_topk_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        const uint32_t blocks = std::max<uint32_t>(1, (nq + qb - 1) / qb);   // at least one block: the flag must be published even for an empty batch
+        const uint32_t work = qb * parts * k, threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
+        k_merge_topk_rank<<<blocks, threads, smem, st>>>(parts, nq, k, qb, part_keys, part_dist, flags, my_part, epoch, keys_out, dist_out);
+        return cudaGetLastError();
+    }
     const uint32_t threads = 128, qpb = threads / 32;
     const size_t smem = (size_t)qpb * parts * k * 12;
     const uint32_t blocks = std::max<uint32_t>(1, (nq + qpb - 1) / qpb);   // at least one block: the flag must be published even for an empty batch

@@ -286,6 +286,20 @@ vs_status vs_search_batch_device(vs_index* ix, size_t nq, const float* d_q, size
     return VS_OK;
 }
 
+vs_status vs_search_batch_fanout_device(vs_index* ix, size_t nq, const float* d_q, size_t k, size_t ef, size_t n_out,
+                                        uint64_t* const* d_keys, float* const* d_dist, void* stream) {
+    if (!ix || (nq && (!d_q || !d_keys || !d_dist))) return fail(VS_ERR_INVALID, "search: null argument");
+    if (k == 0) return fail(VS_ERR_INVALID, "search: k == 0");
+    if (n_out == 0 || n_out > 9) return fail(VS_ERR_UNSUPPORTED, "search: 1 to 9 result buffers");
+    if (ix->G != 1) return fail(VS_ERR_UNSUPPORTED, "search: result fan-out is for single-device indexes (a multi-device index merges inside the library)");
+    for (size_t i = 0; i < n_out; ++i) if (nq && (!d_keys[i] || !d_dist[i])) return fail(VS_ERR_INVALID, "search: null result buffer");
+    if (nq == 0) return VS_OK;
+    OutFan fan; fan.n = (uint32_t)(n_out - 1);
+    for (size_t i = 1; i < n_out; ++i) { fan.keys[i - 1] = d_keys[i]; fan.dist[i - 1] = d_dist[i]; }
+    Shard* sh = ix->sh[0];
+    return sh->search_device(nq, d_q, k, ef, 0, d_keys[0], d_dist[0], stream ? (cudaStream_t)stream : sh->sstream, stream == nullptr, &fan);
+}
+
 vs_status vs_search_batch(vs_index* ix, size_t nq, const float* qs, size_t k, size_t ef, int exact,
                           uint64_t* keys_out, float* dist_out, size_t* found) {
     if (!ix || (nq && (!qs || !keys_out || !dist_out))) return fail(VS_ERR_INVALID, "search: null argument");

@@ -106,8 +106,10 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
                             uint32_t* out_slots, uint64_t* out_keys, float* out_dist,
                             const ExactScratch& scratch, const ExactScratch& fb_scratch, const DeviceInfo& dev, cudaStream_t st, TcStats* stats);
 
+// up to 8 more copies of every result list (peer memory in the sharded search); plain data, passed to the kernels by value
+struct OutFan { uint32_t n = 0; uint64_t* keys[8] = {}; float* dist[8] = {}; };
 cudaError_t launch_search(const GraphView& g, const float* d_queries, uint32_t nq, uint32_t k, uint32_t ef, const DeviceInfo& dev,
-                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st);
+                          uint64_t* d_keys, float* d_dist, unsigned long long* counters, cudaStream_t st, const OutFan* fan = nullptr);
 uint32_t build_efp(uint32_t ef);
 cudaError_t launch_build_search(const GraphView& g, const BuildBatch& b, uint32_t ef, const DeviceInfo& dev,
                                 unsigned long long* counters, cudaStream_t st);

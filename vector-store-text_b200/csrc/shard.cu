@@ -599,8 +599,10 @@ vs_status Shard::compact_locked() {
 
 // ---- search --------------------------------------------------------------------------------------------------------
 // device-accessible queries/outputs on stream st. ANN needs no scratch; exact mode uses the search-side scratch under search_mu.
-vs_status Shard::search_device(size_t nq, const float* d_q, size_t k, size_t ef, int exact, uint64_t* d_keys, float* d_dist, cudaStream_t st, bool sync) {
+vs_status Shard::search_device(size_t nq, const float* d_q, size_t k, size_t ef, int exact, uint64_t* d_keys, float* d_dist, cudaStream_t st, bool sync,
+                               const OutFan* fan) {
     if (nq == 0) return VS_OK;
+    if (fan && fan->n && exact) return fail(VS_ERR_UNSUPPORTED, "search: result fan-out is for the graph search (exact = 0) only");
     maybe_flush_nonblocking();
     cudaSetDevice(dev.device);
     std::shared_lock<std::shared_mutex> rd(tables);
@@ -646,8 +648,9 @@ vs_status Shard::search_device(size_t nq, const float* d_q, size_t k, size_t ef,
     uint32_t efe = (uint32_t)std::max(ef ? ef : (size_t)efS, k);
     if (vis > lv && lv > 0) efe = (uint32_t)std::min<uint64_t>(1024, ((uint64_t)efe * vis + lv - 1) / lv);
     GraphView g = view(vis, top);
-    cudaError_t e = launch_search(g, d_q, (uint32_t)nq, (uint32_t)k, efe, dev, d_keys, d_dist, ctr, st);
+    cudaError_t e = launch_search(g, d_q, (uint32_t)nq, (uint32_t)k, efe, dev, d_keys, d_dist, ctr, st, fan);
     if (e == cudaErrorInvalidConfiguration) return fail(VS_ERR_UNSUPPORTED, "search: ef / dims too large for one warp's shared memory");
+    if (e == cudaErrorNotSupported) { cudaGetLastError(); return fail(VS_ERR_UNSUPPORTED, "search: result fan-out needs the staged traversal kernels (rows too long for the staging area)"); }
     CU(e);
     return finish();
 }

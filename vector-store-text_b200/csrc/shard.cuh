@@ -134,7 +134,8 @@ struct Shard {
     size_t count();                                                                 // flush, then live
     // ---- search --------------------------------------------------------------------------------------------
     // device-accessible queries / outputs on stream `st` (never null); sync: wait for completion before returning
-    vs_status search_device(size_t nq, const float* d_q, size_t k, size_t ef, int exact, uint64_t* d_keys, float* d_dist, cudaStream_t st, bool sync);
+    vs_status search_device(size_t nq, const float* d_q, size_t k, size_t ef, int exact, uint64_t* d_keys, float* d_dist, cudaStream_t st, bool sync,
+                            const OutFan* fan = nullptr);
     vs_status search_host(size_t nq, const float* qs, size_t k, size_t ef, int exact, uint64_t* keys_out, float* dist_out, size_t* found);
     // ---- misc ----------------------------------------------------------------------------------------------
     vs_status get_stats(vs_stats* o);

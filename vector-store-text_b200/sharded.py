@@ -23,15 +23,20 @@ from ._ffi import VsIndex, merge_topk_device, merge_topk_flags_device, merge_top
 
 
 class PeerExchange:
-    """Fused barrier + gather + merge over peer memory for `nq` x `k` result lists per rank.
+    """Fused barrier + merge over peer memory for `nq` x `k` result lists per rank.
 
-    Every rank owns two buffers in symmetric memory (keys u64 [nq, k] then dists f32 [nq, k]) and one flag word, all mapped
-    into every peer. A step writes its shard's lists into buffer `turn` (the traversal kernel does so directly) and calls
-    `merge()`: ONE launch of csrc k_merge_topk_ptrs, which publishes this rank's flag = step number (release, system scope),
-    waits for every peer's flag (acquire loads over NVLink), then pulls all peers' lists of a query into shared memory in one
-    round of NVLink loads and merges them. The buffers alternate, so one flag per rank is enough: a rank that has seen a
-    peer's flag i+1 knows that peer has finished merge i. `VSANN_P2P_FLAGS=0` selects the older form (torch's symmetric-memory
-    barrier kernel, then the merge kernel). Raises if symmetric memory cannot be set up (callers fall back to all_gather)."""
+    Every rank owns two buffers in symmetric memory and one flag word, all mapped into every peer. A buffer holds one slot of
+    (keys u64 [nq, k], dists f32 [nq, k]) PER RANK. A step has the shard's lists written into slot `rank` of buffer `turn` and
+    calls `merge()`: ONE launch of the merge kernel, which publishes this rank's flag = step number (release, system scope),
+    waits for every peer's flag (acquire loads over NVLink, one lane per peer), and merges.
+      push (default): `search()` hands the traversal kernel the address of slot `rank` in EVERY rank's buffer
+        (vs_search_batch_fanout_device): a query's list goes out over NVLink as soon as the query is done, the transfer hides
+        behind the rest of the traversal, and the merge reads LOCAL memory only;
+      pull (`VSANN_P2P_PUSH=0`, and always for exact searches): the lists are written locally, the merge kernel loads the peers'
+        slots over NVLink.
+    The buffers alternate, so one flag per rank is enough: a rank that has seen a peer's flag i+1 knows that peer has finished
+    merge i. `VSANN_P2P_FLAGS=0` selects torch's symmetric-memory barrier kernel followed by the merge kernel. Raises if symmetric
+    memory cannot be set up (callers fall back to all_gather)."""
 
     def __init__(self, nq, k, device, group=None, lib=None):
         import torch.distributed._symmetric_memory as symm
@@ -40,10 +45,20 @@ class PeerExchange:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.koff = nq * k * 8
-        self.bufs = [symm.empty(nq * k * 12, dtype=torch.uint8, device=device) for _ in range(2)]
+        self.slot = nq * k * 12 + (-(nq * k * 12) % 16)                      # one rank's lists: keys, then dists
+        self.push = os.environ.get("VSANN_P2P_PUSH", "1") != "0" and self.world <= 9
+        self.bufs = [symm.empty(self.slot * self.world, dtype=torch.uint8, device=device) for _ in range(2)]
         self.hdls = [symm.rendezvous(b, group) for b in self.bufs]
-        self.kptr = [torch.tensor([int(p) for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
-        self.dptr = [torch.tensor([int(p) + self.koff for p in h.buffer_ptrs], dtype=torch.int64, device=device) for h in self.hdls]
+        mine = self.rank * self.slot
+        # pull: part p = slot p of RANK p's buffer; push: part p = slot p of MY buffer
+        self.kptr = [torch.tensor([int(p) + r * self.slot for r, p in enumerate(h.buffer_ptrs)], dtype=torch.int64, device=device) for h in self.hdls]
+        self.dptr = [torch.tensor([int(p) + r * self.slot + self.koff for r, p in enumerate(h.buffer_ptrs)], dtype=torch.int64, device=device) for h in self.hdls]
+        self.kptr_local = [torch.tensor([b.data_ptr() + r * self.slot for r in range(self.world)], dtype=torch.int64, device=device) for b in self.bufs]
+        self.dptr_local = [torch.tensor([b.data_ptr() + r * self.slot + self.koff for r in range(self.world)], dtype=torch.int64, device=device) for b in self.bufs]
+        # where MY lists go: my own buffer first (the primary output), then every peer's
+        order = [self.rank] + [r for r in range(self.world) if r != self.rank]
+        self.fan_keys = [[int(h.buffer_ptrs[r]) + mine for r in order] for h in self.hdls]
+        self.fan_dist = [[int(h.buffer_ptrs[r]) + mine + self.koff for r in order] for h in self.hdls]
         self.flags = symm.empty(64, dtype=torch.uint8, device=device)
         self.flags.zero_()
         self.fhdl = symm.rendezvous(self.flags, group)
@@ -51,35 +66,50 @@ class PeerExchange:
         self.use_flags = os.environ.get("VSANN_P2P_FLAGS", "1") != "0"
         self.epoch = 0
         self.turn = 0
+        self.pushed = [False, False]
         torch.cuda.synchronize(device)
         self.fhdl.barrier(channel=0)          # every rank's flag word is zero before anybody publishes
         torch.cuda.synchronize(device)
 
     def describe(self):
+        how = ("result lists pushed to every peer by the traversal kernel (stores over NVLink while it runs), merge from local memory"
+               if self.push else "merge kernel loads the peers' lists from symmetric memory")
         if self.use_flags:
-            return "p2p loads from symmetric memory, barrier fused into the merge kernel (release/acquire flags over NVLink): one launch after the traversal"
-        return "p2p loads from symmetric memory + fused merge kernel (torch symmetric-memory barrier kernel per step)"
+            return how + ", barrier fused into the merge kernel (release/acquire flags over NVLink): one launch after the traversal"
+        return how + " (torch symmetric-memory barrier kernel per step)"
 
     def next_buffer(self):
-        """(index, keys device pointer, dists device pointer) of the buffer this step publishes into."""
+        """(index, keys device pointer, dists device pointer) of this rank's slot in the buffer this step publishes into."""
         i = self.turn
         self.turn ^= 1
-        base = self.bufs[i].data_ptr()
+        self.pushed[i] = False
+        base = self.bufs[i].data_ptr() + self.rank * self.slot
         return i, base, base + self.koff
 
+    def search(self, index, nq, q_ptr, ef=0, exact=False, stream=0):
+        """The shard search of a step through `index` (a VsIndex on this rank's GPU); returns the buffer index for merge()."""
+        i, kp, dp = self.next_buffer()
+        if self.push and not exact:
+            index.search_fanout_device(nq, q_ptr, self.k, self.fan_keys[i], self.fan_dist[i], ef=ef, stream=stream)
+            self.pushed[i] = True
+        else:
+            index.search_device(nq, q_ptr, self.k, kp, dp, ef=ef, exact=exact, stream=stream)
+        return i
+
     def views(self, i):
-        b = self.bufs[i]
-        return b[:self.koff].view(torch.int64).view(self.nq, self.k), b[self.koff:].view(torch.float32).view(self.nq, self.k)
+        b = self.bufs[i][self.rank * self.slot:(self.rank + 1) * self.slot]
+        return b[:self.koff].view(torch.int64).view(self.nq, self.k), b[self.koff:self.koff + self.nq * self.k * 4].view(torch.float32).view(self.nq, self.k)
 
     def merge(self, i, mk, md):
         stream = torch.cuda.current_stream().cuda_stream
+        kptr, dptr = (self.kptr_local[i], self.dptr_local[i]) if self.pushed[i] else (self.kptr[i], self.dptr[i])
         if self.use_flags:
             self.epoch += 1
-            merge_topk_flags_device(self.device.index, self.world, self.nq, self.k, self.kptr[i].data_ptr(), self.dptr[i].data_ptr(),
+            merge_topk_flags_device(self.device.index, self.world, self.nq, self.k, kptr.data_ptr(), dptr.data_ptr(),
                                     self.fptr.data_ptr(), self.rank, self.epoch, mk.data_ptr(), md.data_ptr(), stream=stream, lib=self.lib)
             return mk, md
         self.hdls[i].barrier(channel=0)
-        merge_topk_peers_device(self.device.index, self.world, self.nq, self.k, self.kptr[i].data_ptr(), self.dptr[i].data_ptr(),
+        merge_topk_peers_device(self.device.index, self.world, self.nq, self.k, kptr.data_ptr(), dptr.data_ptr(),
                                 mk.data_ptr(), md.data_ptr(), stream=stream, lib=self.lib)
         return mk, md
 
@@ -165,8 +195,7 @@ class ShardedIndex:
             if px is None and exchange == "p2p":
                 raise RuntimeError("symmetric memory is not available")
             if px is not None:
-                i, kp, dp = px.next_buffer()
-                self.local.search_device(nq, qd.data_ptr(), k, kp, dp, ef=ef, exact=exact, stream=stream)
+                i = px.search(self.local, nq, qd.data_ptr(), ef=ef, exact=exact, stream=stream)
                 mk = torch.empty_like(ok) if mk is None else mk
                 md = torch.empty_like(od) if md is None else md
                 return px.merge(i, mk, md)
