@@ -526,14 +526,6 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    if os.environ.get("VSANN_BENCH_PIN") == "1" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
-        # experiment: every rank on its own slice of the host cores (torchrun does not pin; a migrating launch thread shows up in every
-        # rank's step, because every step ends in a barrier)
-        try:
-            cores = sorted(os.sched_getaffinity(0)); w = int(os.environ["WORLD_SIZE"]); per = max(1, len(cores) // w)
-            os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
-        except Exception:   # noqa: BLE001
-            pass
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -880,17 +872,21 @@ def main():
     e2e_modes = ["in_place"] if (world > 1 and p2p) else ["c_abi_host_buffers"]
     e2e_by_mode = {}
     for mode in e2e_modes:
-        for _ in range(max(1, args.warmup)):
+        for _ in range(max(1, args.warmup) + (10 if world > 1 else 0)):   # (N > 1: the first steps after the device-timed regions still see one-off costs)
             e2e_step(mode)
         barrier()
         gc.collect(); gc.disable()          # a collection inside a 6 ms region would be a tenth of it
         if mode == e2e_modes[0]:
             sampler.mark(True)
+        per_step = []
         t0 = time.perf_counter()
         for _ in range(args.steps):
+            ta = time.perf_counter()
             e2e_step(mode)
+            per_step.append(time.perf_counter() - ta)
         torch.cuda.synchronize()
         e2e_by_mode[mode] = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+        e2e_spread = {"median_ms": max_over_ranks(float(np.median(per_step)) * 1e3), "max_ms": max_over_ranks(float(np.max(per_step)) * 1e3)}
         if mode == e2e_modes[0]:
             sampler.mark(False)
         gc.enable()
@@ -1081,7 +1077,7 @@ def main():
             "parity_at_bench": parity_at_bench,
             "build": build,
             "e2e": {"value": nq / (e2e_ms * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4 * world, "d2h_bytes_per_step": nq * k * 12 * world,
-                    "ms_per_step": e2e_ms, "recall_at_k": e2e_recall, "path": e2e_mode, "ms_per_step_by_path": e2e_by_mode, "breakdown": e2e_breakdown},
+                    "ms_per_step": e2e_ms, "recall_at_k": e2e_recall, "path": e2e_mode, "per_step_spread": e2e_spread, "breakdown": e2e_breakdown},
             "gpu_launches": args.steps * (1 if S == 1 else (G + 1 if G > 1 else 2)),   # per step: k_search_t per shard (+ the merge kernel after the exchange)
             "by_batch": by_batch or None, "recall_sweep": recall_sweep,
             "exact": exact,
