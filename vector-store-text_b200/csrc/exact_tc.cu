@@ -82,6 +82,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// half a corpus tile, delivered to BOTH CTAs of a 2-CTA cluster (same shared-memory offset, same mbarrier offset in each)
+__device__ __forceinline__ void tma_load_2d_mc2(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, FP32 accumulate; issued by ONE thread
@@ -92,6 +101,10 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
 // mbarrier arrive once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// the same arrive on the mbarrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_mc2(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3) : "memory");
 }
 // issue a 32-column load of this thread's accumulator row; tmem_wait() before the registers are read
 __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, float (&v)[32]) {
@@ -162,7 +175,12 @@ __device__ __forceinline__ float2 row_coeffs(const ScanArgs& a, uint32_t r, cons
 
 // R: sampled keys a thread keeps (sampling pass only): the insertion network costs 2 (R - 1) instructions per accepted key, and a
 // key accepted by ONE of a warp's 32 queries is paid for by all of them
-template <bool EMIT, int R>
+// CL: launched as clusters of two CTAs along x (two query tiles, the same corpus slice). Each CTA fetches HALF of every corpus tile and
+// the TMA multicasts it into both CTAs' rings, so a tile crosses L2 -> SM once per pair (a third less L2 traffic at d > 128, half at
+// d <= 128 where the queries are resident). A stage is free again when BOTH CTAs' MMAs have read it (the commit arrives on both CTAs'
+// `empty` barriers). mapX then has a box of BN / 2 rows. Measured on B200: 3.51 -> 3.42 ms at 1M x 128 x 10k, no change at d = 768 / 1536
+// (tensor pipe 88-90 % active either way: those scans were not waiting for the L2).
+template <bool EMIT, int R, bool CL = false>
 __global__ void __launch_bounds__(threads_of(EMIT), 1)
 k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapX, const ScanArgs a) {
     extern __shared__ unsigned char smem_raw[];
@@ -181,13 +199,14 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     const uint32_t q0 = blockIdx.x * BM, slice = blockIdx.y;
     // second scan: launched for the largest query count it may see; CTAs past the count the first round left on the device leave at once
     uint32_t nq_eff = a.nq;
-    if (a.n_active) { nq_eff = min(*a.n_active, a.active_cap); if (q0 >= nq_eff) return; }
+    if (a.n_active) { nq_eff = min(*a.n_active, a.active_cap); if ((CL ? (blockIdx.x & ~1u) * BM : q0) >= nq_eff) return; }   // (a pair leaves together)
+    const uint32_t crank = CL ? cluster_ctarank() : 0u;
     const uint32_t t_begin = slice * a.tiles_per_slice, t_end = min(a.n_tiles, t_begin + a.tiles_per_slice);
     const uint32_t t_step = EMIT ? 1u : a.sample_stride;
     const uint32_t t_first = EMIT ? t_begin : ((t_begin + a.sample_stride - 1) / a.sample_stride) * a.sample_stride;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), 1); }
+        for (int i = 0; i < STAGES; ++i) { mbar_init(s32(&ctrl->full[i]), 1); mbar_init(s32(&ctrl->empty[i]), CL ? 2 : 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(s32(&ctrl->tfull[i]), 1); mbar_init(s32(&ctrl->tempty[i]), EW); }
         for (int i = 0; i < CB; ++i) { mbar_init(s32(&ctrl->cfull[i]), 1); mbar_init(s32(&ctrl->cempty[i]), EW); }
         mbar_init(s32(&ctrl->afull), 1);
@@ -199,6 +218,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     }
     tc_fence_before();
     __syncthreads();
+    if (CL) cluster_sync_all();      // the peer's barriers exist before anything of ours can arrive on them
     tc_fence_after();
     const uint32_t tmem_base = ctrl->tmem_base;
 
@@ -228,7 +248,8 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                     mbar_expect_tx(full, res_a ? B_BYTES : STAGE_BYTES);
                     const uint32_t dst = ring_s + stage * stage_bytes;
                     if (!res_a) tma_load_2d(dst, &mapQ, full, (int)(kb * BK), (int)q0);
-                    tma_load_2d(dst + b_off, &mapX, full, (int)(kb * BK), (int)(t * BN));
+                    if (CL) tma_load_2d_mc2(dst + b_off + crank * (uint32_t)(B_BYTES / 2), &mapX, full, (int)(kb * BK), (int)(t * BN + crank * (BN / 2)));
+                    else tma_load_2d(dst + b_off, &mapX, full, (int)(kb * BK), (int)(t * BN));
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -255,7 +276,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
                     if (kb == 0xffffffffu) for (int k = 0; k < 1; ++k)
 #endif
                         umma_tf32(d_tmem, da + (uint64_t)(k * UMMA_K * 4 >> 4), db + (uint64_t)(k * UMMA_K * 4 >> 4), IDESC_TF32, (kb | (uint32_t)k) != 0u);
-                    umma_commit(s32(&ctrl->empty[stage]));      // frees the smem stage once these MMAs are done
+                    if (CL) umma_commit_mc2(s32(&ctrl->empty[stage])); else umma_commit(s32(&ctrl->empty[stage]));      // frees the smem stage once these MMAs are done
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
                 umma_commit(s32(&ctrl->tfull[buf]));              // accumulator ready for the epilogue
@@ -396,6 +417,7 @@ k_tc_scan(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUte
     }
     tc_fence_before();
     __syncthreads();
+    if (CL) cluster_sync_all();      // the peer may still be arriving on this CTA's barriers
     if (warp == W_MMA) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
@@ -689,7 +711,7 @@ static bool make_map(CUtensorMap* m, const float* base, uint64_t rows, uint32_t 
     return make_tmap_f32(m, base, rows, dpad, row_stride_floats, BK, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
-struct Plan { uint32_t nqt, nq_pad, n_tiles, slices, tiles_per_slice, s_slices, s_tiles_per_slice, kblocks, stride, r, cap, kp; bool ok; };
+struct Plan { uint32_t nqt, nqt_launch, nq_pad, n_tiles, slices, tiles_per_slice, s_slices, s_tiles_per_slice, kblocks, stride, r, cap, kp; bool ok, cluster; };
 
 // r-th smallest of a 1/stride sample as threshold: expected stride * r rows pass, P(fewer than k pass) < 1e-3
 static uint32_t sample_rank(uint32_t k, uint32_t stride) {
@@ -712,13 +734,17 @@ static uint32_t pick_slices(uint32_t nqt, uint32_t lo, uint32_t hi, int sm_count
 static Plan make_plan(uint32_t nq, uint32_t n, uint32_t k, uint32_t dpad, int sm_count) {
     Plan p;
     p.nqt = (nq + BM - 1) / BM; p.nq_pad = p.nqt * BM;
+    // full scan as 2-CTA clusters (the corpus tile multicast to both): from two query tiles on; an odd count gets one idle partner
+    static const int cl_env = [] { const char* e = getenv("VSANN_TC_CLUSTER"); return e ? atoi(e) : 1; }();
+    p.cluster = cl_env != 0 && p.nqt >= 2 && (p.nqt % 2 == 0 || p.nqt >= 32);   // (an idle partner is 1 / nqt of wasted MMAs)
+    p.nqt_launch = p.cluster ? (p.nqt + 1u) & ~1u : p.nqt;
     p.n_tiles = (n + BN - 1) / BN;
     p.kblocks = (dpad + BK - 1) / BK;
-    uint32_t want = (8u * (uint32_t)sm_count + p.nqt - 1) / p.nqt;          // ~8 waves of CTAs
+    uint32_t want = (8u * (uint32_t)sm_count + p.nqt_launch - 1) / p.nqt_launch;          // ~8 waves of CTAs
     want = std::min<uint32_t>(want, std::max<uint32_t>(1u, p.n_tiles / 8));   // >= 8 tiles per CTA
     // (a cap of 64 slices left 64 of 148 SMs busy for a single query tile: 2.3 TB/s at 5M x 1536, B <= 128)
     want = std::max<uint32_t>(1u, std::min<uint32_t>(want, 1024u));
-    want = pick_slices(p.nqt, std::max<uint32_t>(1u, (want + 1) / 2), want, sm_count);
+    want = pick_slices(p.nqt_launch, std::max<uint32_t>(1u, (want + 1) / 2), want, sm_count);
     p.tiles_per_slice = std::max<uint32_t>(1u, (p.n_tiles + want - 1) / want);
     p.slices = (p.n_tiles + p.tiles_per_slice - 1) / p.tiles_per_slice;
     // sampling stride: 32 on large corpora (the sample pass is the slow one per tile), denser on small ones so
@@ -800,6 +826,7 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     TC_TRY(cudaFuncSetAttribute(k_tc_scan<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     TC_TRY(cudaFuncSetAttribute(k_tc_scan<false, R_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     TC_TRY(cudaFuncSetAttribute(k_tc_scan<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    TC_TRY((cudaFuncSetAttribute(k_tc_scan<true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)));
     const size_t dsmem = (size_t)q.dpad * 4 + 4 * 32 * 33 * 4, ssmem = 4 * ((size_t)p.kp * 16 + 256);
     if (dsmem > dev.smem_per_block) return cudaErrorInvalidConfiguration;
     TC_TRY(cudaFuncSetAttribute(k_tc_exact_dist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem));
@@ -830,7 +857,18 @@ cudaError_t launch_exact_tc(const ExactCorpus& c, const ExactQueries& q, int met
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     const bool timing = stats && stats->time_scan && cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess;
     if (timing) cudaEventRecord(ev0, st);
-    k_tc_scan<true, 1><<<grid, threads_of(true), SMEM_BYTES, st>>>(mapQ, mapX, a);
+    if (p.cluster) {
+        CUtensorMap mapXh;
+        if (!make_map(&mapXh, c.vecs, c.n, q.dpad, c.row_stride, BN / 2)) return cudaErrorNotSupported;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(p.nqt_launch, p.slices); cfg.blockDim = dim3(threads_of(true)); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        TC_TRY(cudaLaunchKernelEx(&cfg, k_tc_scan<true, 1, true>, mapQ, mapXh, a));
+    } else {
+        k_tc_scan<true, 1><<<grid, threads_of(true), SMEM_BYTES, st>>>(mapQ, mapX, a);
+    }
     if (timing) cudaEventRecord(ev1, st);
     if (a.flags & 24u) {   // rate measurement (bench.py: tcgen05 TF32 rate of this kernel without its epilogue / without its loads): nothing to re-rank
         TC_TRY(cudaStreamSynchronize(st));
